@@ -1,0 +1,178 @@
+/*
+ * sphb200.h -- C ABI of the B200-native SPH step engine (libsphb200.so).
+ *
+ * This is the drop-in boundary for the one hot path of Dimitime/SPH: the per-step
+ *   update_density -> update_forces -> update_posvel -> collision
+ * sequence that SPH/main.cpp:293-300 (step_scene) runs on the CPU through class SphUtils
+ * (SPH/SphUtils.hpp:16-44).  Everything here is extern "C": opaque handle, plain pointers and sizes,
+ * int status codes.  All compute runs in hand-written CUDA kernels (sm_100a); there is no CPU path.
+ *
+ * Host exchange format = the reference's own records, byte for byte:
+ *   Particle  52 B  pos@0 vel@12 accel@24 mass@36 density@40 pressure@44 thermal@48   (SPH/Particle.hpp:42-50)
+ *   Wall      32 B  normal@0 center@12 xlength@24 ylength@28                           (SPH/Wall.hpp:28-31)
+ *   Sphere    44 B  pos@0 vel@12 accel@24 radius@36 mass@40                            (SPH/Sphere.hpp:29-33)
+ *
+ * Threading: one engine per GPU, calls on one engine from one thread at a time (the reference is
+ * single-threaded, main.cpp idle()/keyboard() callbacks).  Different engines are independent.
+ */
+#ifndef SPHB200_H
+#define SPHB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPHB_OK 0
+#define SPHB_ERR_INVALID 1   /* bad argument */
+#define SPHB_ERR_CUDA 2      /* a CUDA runtime call failed; see sphb_last_error() */
+#define SPHB_ERR_STATE 3     /* call out of order (e.g. step before upload) */
+#define SPHB_ERR_CAPACITY 4  /* a fixed capacity was exceeded */
+
+#define SPHB_MAX_WALLS 16
+
+/* field_mask bits for sphb_download_aos / sphb_step_aos */
+#define SPHB_F_POS 1u
+#define SPHB_F_VEL 2u
+#define SPHB_F_ACCEL 4u
+#define SPHB_F_DENSITY 8u  /* density and pressure */
+#define SPHB_F_ALL 15u
+
+/* domain_mode */
+#define SPHB_DOMAIN_BBOX 0  /* grid origin = bounding-box minimum of the particles, recomputed on the device every
+                               step: the behaviour of update_cells, SPH/SphUtils.cpp:11-27 */
+#define SPHB_DOMAIN_FIXED 1 /* grid covers [domain_lo, domain_hi]; cell coordinates are clamped to it */
+
+typedef struct sphb_engine sphb_engine;
+
+/*
+ * Solver constants.  The first five are the SphUtils constructor's arguments (SPH/SphUtils.hpp:20-29;
+ * main.cpp:30-41 passes h=0.45, rho0=10, c=100, dt=0.033, eps=0.01).  The rest are literals that the
+ * reference hard-codes in SphUtils.cpp; sphb_default_params() sets them to those literals.
+ */
+typedef struct sphb_params {
+    float h;               /* smooth_length.  NOTE the support radius is h*h (SphUtils.cpp:57-61: q=r/h compared to h) */
+    float rho0;            /* rest density; density is clamped UP to it (SphUtils.cpp:141-142) */
+    float c;               /* stored, never read by the reference */
+    float dt;              /* time step (SphUtils.cpp:326-328) */
+    float eps;             /* stored, never read by the reference */
+    float eos_k;           /* 100.0f: pressure = eos_k*(density-rho0)            (SphUtils.cpp:144) */
+    float gravity[3];      /* (0,-1,0)                                           (SphUtils.cpp:298) */
+    float visc_alpha;      /* 0.1f  artificial viscosity, linear term            (SphUtils.cpp:226) */
+    float visc_beta;       /* 0.2f  quadratic term                               (SphUtils.cpp:226) */
+    float visc_eta;        /* 0.01f: mu denominator r*r + eta*h*h                (SphUtils.cpp:225) */
+    float restitution;     /* 0.0f: impulse factor (1+restitution)               (SphUtils.cpp:352) */
+    float cell_size;       /* grid cell edge; 0 => support radius h*h.  Must be >= h*h/2 */
+    double wall_test_off;  /* 0.001: hit if dot - off <= wall_test_lim, compared in double like the reference's
+                              double literals                                    (SphUtils.cpp:349) */
+    double wall_test_lim;  /* 0.01 */
+    int32_t domain_mode;   /* SPHB_DOMAIN_* */
+    float domain_lo[3];    /* used when domain_mode == SPHB_DOMAIN_FIXED */
+    float domain_hi[3];
+    int32_t periodic[3];   /* per axis: 1 => minimum-image wrap over [domain_lo, domain_hi) (needs FIXED). Extension:
+                              the reference has only planes */
+    int64_t max_cells;     /* capacity of the cell table; 0 => chosen from the particle count at upload */
+    int32_t write_accel;   /* 1 => sphb_step also stores per-particle acceleration (parity / viewers); 0 => skipped */
+    int32_t reserved[7];
+} sphb_params;
+
+/* Fill *p with the reference's constants (main.cpp:30-41 and the literals of SphUtils.cpp). */
+void sphb_default_params(sphb_params* p);
+
+/* Last error message of the calling thread ("" if none). */
+const char* sphb_last_error(void);
+
+/* Library / build identification, e.g. "sphb200 0.1 sm_100a". */
+const char* sphb_version(void);
+
+/* sizeof(sphb_params) as the library was built: lets a foreign-language binding check its struct layout. */
+size_t sphb_params_size(void);
+
+/* Replaces `SphUtils sph(h, rho0, c, dt, eps)` (main.cpp:62, SphUtils.hpp:20-29).  device = CUDA ordinal. */
+int sphb_create(const sphb_params* p, int device, sphb_engine** out);
+void sphb_destroy(sphb_engine* e);
+
+/* Walls as the `walls` vector of collision() (SphUtils.cpp:343-372, main.cpp:508-540), in vector order.
+ * `walls` points at `count` records of `stride` bytes whose first six floats are normal.xyz, center.xyz
+ * (stride 32 for the reference's Wall, 24 for packed floats).  count <= SPHB_MAX_WALLS. */
+int sphb_set_walls(sphb_engine* e, const void* walls, size_t count, size_t stride);
+
+/* Host AoS -> device SoA.  `particles` points at n records of `stride` bytes laid out like the
+ * reference's Particle (stride 52).  pos, vel, mass are taken; accel, density, pressure are taken too so
+ * that a single phase can be run on a state produced elsewhere.  n may change between calls
+ * (main.cpp:441 grows the vector).  Particle order is remembered: downloads return it. */
+int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stride);
+
+/* Device SoA -> host AoS, original order, only the fields in field_mask are written. */
+int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask);
+
+/* --- the five public methods of SphUtils (SPH/SphUtils.hpp:40-44), on the device-resident state ---- */
+
+/* update_cells (SphUtils.cpp:8-47): bounding box, cell coordinates, stable counting sort; the state is
+ * permuted into cell order.  Called implicitly by sphb_update_density when positions changed. */
+int sphb_update_cells(sphb_engine* e);
+/* update_density (SphUtils.cpp:100-149): rho_i = sum_{j != i} m_j W_ij, clamp up to rho0, P = k(rho - rho0). */
+int sphb_update_density(sphb_engine* e);
+/* update_forces (SphUtils.cpp:157-239, 295-304): accel = gravity + pressure/artificial-viscosity pair sum. */
+int sphb_update_forces(sphb_engine* e);
+/* update_posvel (SphUtils.cpp:321-335): vel += dt*accel; pos += dt*vel. */
+int sphb_update_posvel(sphb_engine* e);
+/* collision (SphUtils.cpp:343-372), wall part: sequential plane test/response per particle. */
+int sphb_collision(sphb_engine* e);
+
+/* step_scene (main.cpp:280-303) x nsteps, fused fast path: sort, density, then ONE kernel doing
+ * force + integrate + wall collision.  Asynchronous: returns after enqueueing; use sphb_synchronize. */
+int sphb_step(sphb_engine* e, int nsteps);
+
+/* The whole reference-facing call on HOST buffers: upload, nsteps steps, download(field_mask), synchronised. */
+int sphb_step_aos(sphb_engine* e, void* particles, size_t n, size_t stride, int nsteps, uint32_t field_mask);
+
+int sphb_synchronize(sphb_engine* e);
+
+/* Page-lock / release a host range (e.g. the std::vector<Particle> buffer the viewer owns) so that
+ * uploads and downloads run at full PCIe rate.  Optional: pageable memory works, slower. */
+int sphb_host_register(void* ptr, size_t bytes);
+int sphb_host_unregister(void* ptr);
+
+/* kernel_function / grad_kernel / lap_kernel (SphUtils.cpp:55-95) evaluated ON THE DEVICE with the same
+ * device functions the step kernels use, for `count` point pairs.  xi, xj: 3*count floats (host).
+ * Any of w (count), grad (3*count), lap (count) may be NULL. */
+int sphb_eval_kernels(sphb_engine* e, const float* xi, const float* xj, size_t count, float* w, float* grad, float* lap);
+
+/* Grid of the last sort, for the bit-exact grid test: cell_xyz[3n] in ORIGINAL particle order,
+ * perm[n] = original index held by sorted slot s, dims[3], origin[3], cell size.  Any may be NULL. */
+int sphb_get_cells(sphb_engine* e, int32_t* cell_xyz, int32_t* perm, int32_t* dims, float* origin, float* cell);
+
+/* Bounding box {minx,miny,minz,maxx,maxy,maxz} of the current positions (SphUtils.cpp:11-23). */
+int sphb_get_bbox(sphb_engine* e, float bbox[6]);
+
+size_t sphb_count(const sphb_engine* e);
+
+/* Per-phase GPU time, measured with CUDA events on the engine's stream around the kernels of each
+ * sphb_step step (no host synchronisation is added).  sphb_enable_timing(e, 1) starts (and resets) the
+ * record, up to 256 steps; sphb_get_timing synchronises and returns the AVERAGE ms per step over the
+ * recorded steps: [0] grid+sort+reorder, [1] density, [2] force+integrate+collide, [3] whole step;
+ * *steps (may be NULL) = how many steps were averaged. */
+int sphb_enable_timing(sphb_engine* e, int on);
+int sphb_get_timing(sphb_engine* e, float ms[4], int* steps);
+
+/* Kernel launches issued by this engine since creation (for bench.py's gpu_launches). */
+uint64_t sphb_launch_count(const sphb_engine* e);
+
+/* --- device-resident access for the headless bench and the multi-GPU driver ----------------------- */
+
+/* Upload from DEVICE SoA arrays (float4 posm = x,y,z,mass; float4 vel = vx,vy,vz,0), n particles,
+ * device-to-device on the engine's stream.  ids (may be NULL) = caller's 32-bit particle ids. */
+int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, const int32_t* ids, size_t n);
+/* Current device pointers (sorted order, valid until the next call that steps or uploads):
+ * posm float4, vel float4, aux float4 (density, pressure, sqrt|P/rho|, 1/rho), accel float4, ids int32. */
+int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, void** accel, int32_t** ids);
+/* The CUDA stream (cudaStream_t) all of this engine's work is enqueued on. */
+void* sphb_stream(sphb_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPHB200_H */

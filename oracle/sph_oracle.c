@@ -300,7 +300,8 @@ typedef struct {
 void orc_grid_from_bbox(const float bbox[6], float cell, long long max_cells, orc_grid* g) {
     for (int a = 0; a < 3; a++) {
         g->origin[a] = bbox[a];
-        g->dims[a] = (int)ceilf((bbox[3 + a] - bbox[a]) / cell) + 1;
+        float ext = ceilf((bbox[3 + a] - bbox[a]) / cell);
+        g->dims[a] = (ext < 1048575.0f) ? (int)ext + 1 : 1048576; /* cap also catches inf/NaN extents */
         if (g->dims[a] < 1) g->dims[a] = 1;
     }
     g->cell = cell;

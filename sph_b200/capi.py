@@ -1,0 +1,269 @@
+"""ctypes binding of libsphb200.so (include/sphb200.h) -- the only way Python reaches the engine.
+
+There is no Python or CPU implementation behind these calls: if the shared library is missing or a
+call fails, an exception is raised.  The reference-side equivalent of this file is the cgo/ctypes
+stub shown in INTEGRATION.md.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsphb200.so")
+
+# Host exchange records, byte-compatible with the reference:
+# SPH/Particle.hpp:42-50 (52 B), SPH/Wall.hpp:28-31 (32 B), SPH/Sphere.hpp:29-33 (44 B)
+PARTICLE = np.dtype(
+    [("pos", "<f4", 3), ("vel", "<f4", 3), ("accel", "<f4", 3), ("mass", "<f4"), ("density", "<f4"),
+     ("pressure", "<f4"), ("thermal", "<f4")]
+)
+WALL = np.dtype([("normal", "<f4", 3), ("center", "<f4", 3), ("xlength", "<f4"), ("ylength", "<f4")])
+SPHERE = np.dtype([("pos", "<f4", 3), ("vel", "<f4", 3), ("accel", "<f4", 3), ("radius", "<f4"), ("mass", "<f4")])
+
+F_POS, F_VEL, F_ACCEL, F_DENSITY, F_ALL = 1, 2, 4, 8, 15
+DOMAIN_BBOX, DOMAIN_FIXED = 0, 1
+
+
+class SphbError(RuntimeError):
+    pass
+
+
+class Params(C.Structure):
+    """struct sphb_params (include/sphb200.h)."""
+
+    _fields_ = [
+        ("h", C.c_float), ("rho0", C.c_float), ("c", C.c_float), ("dt", C.c_float), ("eps", C.c_float),
+        ("eos_k", C.c_float), ("gravity", C.c_float * 3),
+        ("visc_alpha", C.c_float), ("visc_beta", C.c_float), ("visc_eta", C.c_float),
+        ("restitution", C.c_float), ("cell_size", C.c_float),
+        ("wall_test_off", C.c_double), ("wall_test_lim", C.c_double),
+        ("domain_mode", C.c_int32), ("domain_lo", C.c_float * 3), ("domain_hi", C.c_float * 3),
+        ("periodic", C.c_int32 * 3), ("max_cells", C.c_int64), ("write_accel", C.c_int32),
+        ("reserved", C.c_int32 * 7),
+    ]
+
+
+EXPORTS = [
+    "sphb_default_params", "sphb_last_error", "sphb_version", "sphb_params_size", "sphb_create", "sphb_destroy", "sphb_set_walls",
+    "sphb_upload_aos", "sphb_download_aos", "sphb_update_cells", "sphb_update_density", "sphb_update_forces",
+    "sphb_update_posvel", "sphb_collision", "sphb_step", "sphb_step_aos", "sphb_synchronize",
+    "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
+    "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
+    "sphb_get_device_state", "sphb_stream",
+]
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load libsphb200.so.  Fails loudly: there is no fallback implementation."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SphbError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C sph_b200/csrc`).  sph_b200 has no CPU or PyTorch fallback."
+        )
+    L = C.CDLL(LIB_PATH)
+    vp, sz, u32, i32 = C.c_void_p, C.c_size_t, C.c_uint32, C.c_int
+    L.sphb_default_params.argtypes = [C.POINTER(Params)]
+    L.sphb_default_params.restype = None
+    L.sphb_last_error.restype = C.c_char_p
+    L.sphb_version.restype = C.c_char_p
+    L.sphb_params_size.restype = sz
+    if L.sphb_params_size() != C.sizeof(Params):
+        raise SphbError(f"sphb_params layout mismatch: library {L.sphb_params_size()} B, binding {C.sizeof(Params)} B")
+    L.sphb_create.argtypes = [C.POINTER(Params), i32, C.POINTER(vp)]
+    L.sphb_destroy.argtypes = [vp]
+    L.sphb_destroy.restype = None
+    L.sphb_set_walls.argtypes = [vp, vp, sz, sz]
+    L.sphb_upload_aos.argtypes = [vp, vp, sz, sz]
+    L.sphb_download_aos.argtypes = [vp, vp, sz, sz, u32]
+    for name in ("sphb_update_cells", "sphb_update_density", "sphb_update_forces", "sphb_update_posvel",
+                 "sphb_collision", "sphb_synchronize"):
+        getattr(L, name).argtypes = [vp]
+    L.sphb_step.argtypes = [vp, i32]
+    L.sphb_step_aos.argtypes = [vp, vp, sz, sz, i32, u32]
+    L.sphb_host_register.argtypes = [vp, sz]
+    L.sphb_host_unregister.argtypes = [vp]
+    L.sphb_eval_kernels.argtypes = [vp, vp, vp, sz, vp, vp, vp]
+    L.sphb_get_cells.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.sphb_get_bbox.argtypes = [vp, vp]
+    L.sphb_count.argtypes = [vp]
+    L.sphb_count.restype = sz
+    L.sphb_enable_timing.argtypes = [vp, i32]
+    L.sphb_get_timing.argtypes = [vp, vp, vp]
+    L.sphb_launch_count.argtypes = [vp]
+    L.sphb_launch_count.restype = C.c_uint64
+    L.sphb_upload_soa_device.argtypes = [vp, vp, vp, vp, sz]
+    L.sphb_get_device_state.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    L.sphb_stream.argtypes = [vp]
+    L.sphb_stream.restype = vp
+    _lib = L
+    return L
+
+
+def default_params(**overrides) -> Params:
+    L = load_library()
+    p = Params()
+    L.sphb_default_params(C.byref(p))
+    for k, v in overrides.items():
+        cur = getattr(p, k)
+        if isinstance(cur, C.Array):
+            for i, x in enumerate(v):
+                cur[i] = x
+        else:
+            setattr(p, k, v)
+    return p
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Engine:
+    """Thin object wrapper over the C ABI; one instance = one sphb_engine on one GPU."""
+
+    def __init__(self, params: Params | None = None, device: int = 0, **overrides):
+        self.lib = load_library()
+        self.params = params if params is not None else default_params(**overrides)
+        h = C.c_void_p()
+        self._check(self.lib.sphb_create(C.byref(self.params), device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise SphbError(f"sphb error {rc}: {self.lib.sphb_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.sphb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # --- state
+    def set_walls(self, walls: np.ndarray):
+        walls = np.ascontiguousarray(walls)
+        if walls.dtype == WALL:
+            self._check(self.lib.sphb_set_walls(self.h, _ptr(walls), len(walls), WALL.itemsize))
+        else:
+            w = np.ascontiguousarray(walls, np.float32).reshape(-1, 6)
+            self._check(self.lib.sphb_set_walls(self.h, _ptr(w), len(w), 24))
+
+    def upload(self, particles: np.ndarray):
+        assert particles.dtype == PARTICLE and particles.flags.c_contiguous
+        self._check(self.lib.sphb_upload_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize))
+
+    def download(self, particles: np.ndarray, mask: int = F_ALL):
+        assert particles.dtype == PARTICLE and particles.flags.c_contiguous
+        self._check(self.lib.sphb_download_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize, mask))
+        return particles
+
+    def upload_ptr(self, ptr: int, n: int, stride: int = 52):
+        self._check(self.lib.sphb_upload_aos(self.h, C.c_void_p(ptr), n, stride))
+
+    def download_ptr(self, ptr: int, n: int, stride: int = 52, mask: int = F_ALL):
+        self._check(self.lib.sphb_download_aos(self.h, C.c_void_p(ptr), n, stride, mask))
+
+    def upload_soa_device(self, posm_ptr: int, vel_ptr: int, n: int, ids_ptr: int | None = None):
+        self._check(self.lib.sphb_upload_soa_device(self.h, C.c_void_p(posm_ptr), C.c_void_p(vel_ptr),
+                                                    C.c_void_p(ids_ptr) if ids_ptr else None, n))
+
+    # --- the SphUtils methods
+    def update_cells(self):
+        self._check(self.lib.sphb_update_cells(self.h))
+
+    def update_density(self):
+        self._check(self.lib.sphb_update_density(self.h))
+
+    def update_forces(self):
+        self._check(self.lib.sphb_update_forces(self.h))
+
+    def update_posvel(self):
+        self._check(self.lib.sphb_update_posvel(self.h))
+
+    def collision(self):
+        self._check(self.lib.sphb_collision(self.h))
+
+    def step(self, nsteps: int = 1):
+        self._check(self.lib.sphb_step(self.h, nsteps))
+
+    def step_aos(self, particles: np.ndarray, nsteps: int = 1, mask: int = F_ALL):
+        assert particles.dtype == PARTICLE and particles.flags.c_contiguous
+        self._check(self.lib.sphb_step_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize, nsteps, mask))
+
+    def step_aos_ptr(self, ptr: int, n: int, nsteps: int = 1, mask: int = F_ALL, stride: int = 52):
+        self._check(self.lib.sphb_step_aos(self.h, C.c_void_p(ptr), n, stride, nsteps, mask))
+
+    def synchronize(self):
+        self._check(self.lib.sphb_synchronize(self.h))
+
+    # --- diagnostics
+    def eval_kernels(self, xi, xj):
+        xi = np.ascontiguousarray(xi, np.float32).reshape(-1, 3)
+        xj = np.ascontiguousarray(xj, np.float32).reshape(-1, 3)
+        n = len(xi)
+        w = np.zeros(n, np.float32)
+        g = np.zeros((n, 3), np.float32)
+        lap = np.zeros(n, np.float32)
+        self._check(self.lib.sphb_eval_kernels(self.h, _ptr(xi), _ptr(xj), n, _ptr(w), _ptr(g), _ptr(lap)))
+        return w, g, lap
+
+    def get_cells(self):
+        n = self.count()
+        xyz = np.zeros((n, 3), np.int32)
+        perm = np.zeros(n, np.int32)
+        dims = np.zeros(3, np.int32)
+        origin = np.zeros(3, np.float32)
+        cell = np.zeros(1, np.float32)
+        self._check(self.lib.sphb_get_cells(self.h, _ptr(xyz), _ptr(perm), _ptr(dims), _ptr(origin), _ptr(cell)))
+        return xyz, perm, dims, origin, float(cell[0])
+
+    def get_bbox(self) -> np.ndarray:
+        b = np.zeros(6, np.float32)
+        self._check(self.lib.sphb_get_bbox(self.h, _ptr(b)))
+        return b
+
+    def count(self) -> int:
+        return int(self.lib.sphb_count(self.h))
+
+    def enable_timing(self, on: bool = True):
+        self._check(self.lib.sphb_enable_timing(self.h, int(on)))
+
+    def get_timing(self):
+        """(ms[4] averaged per step: sort, density, force+integrate+collide, whole step; steps averaged)."""
+        t = np.zeros(4, np.float32)
+        k = C.c_int(0)
+        self._check(self.lib.sphb_get_timing(self.h, _ptr(t), C.byref(k)))
+        return t, k.value
+
+    def launch_count(self) -> int:
+        return int(self.lib.sphb_launch_count(self.h))
+
+    def device_state(self):
+        ps = [C.c_void_p() for _ in range(5)]
+        self._check(self.lib.sphb_get_device_state(self.h, *[C.byref(p) for p in ps]))
+        return tuple(p.value for p in ps)
+
+    def stream(self) -> int:
+        return int(self.lib.sphb_stream(self.h) or 0)

@@ -1,0 +1,628 @@
+// Device-side code of the SPH step engine: grid build (cell keys, stable counting sort, reorder),
+// density/pressure, fused force+integrate+collide, AoS<->SoA conversion.  sm_100a only.
+//
+// Reference restated (not ported: the reference is a scalar all-pairs CPU loop):
+//   SPH/SphUtils.cpp:8-47   update_cells      -> k_bbox, k_grid_setup, k_key_hist, k_scan_*, k_scatter, k_rank_gather
+//   SPH/SphUtils.cpp:55-95  W, gradW, lapW    -> w_shape(), grad_shape(), k_eval_kernels
+//   SPH/SphUtils.cpp:100-149 update_density   -> k_density
+//   SPH/SphUtils.cpp:157-239,295-304 forces   -> k_force<...>
+//   SPH/SphUtils.cpp:321-335 update_posvel    -> integrate()
+//   SPH/SphUtils.cpp:343-372 collision (walls)-> collide_walls()
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sphb {
+
+constexpr int kMaxWalls = 16;
+
+// Device-resident description of the uniform grid (rebuilt every step by k_grid_setup).
+struct GridDesc {
+    float origin[3];
+    float cell[3]; // per axis (equal unless an axis is periodic and the cell was stretched to tile it)
+    int dims[3];
+    int ncell;     // dims[0]*dims[1]*dims[2]
+    int stencil;   // half width in cells: ceil(R / cell) (1 when cell >= R)
+    int pad;
+};
+
+// Bounding-box accumulator: floats mapped to order-preserving unsigned ints so atomicMin/Max work.
+struct BBoxAcc {
+    unsigned int lo[3];
+    unsigned int hi[3];
+};
+
+// Everything the physics kernels need, passed by value (lives in the kernel parameter space).
+struct Consts {
+    float h, h2, inv_h, inv_h2; // h2 = h*h (the support radius R), inv_h2 = 1/(h*h)
+    float R2;                   // R*R: a pair interacts iff d2 < R2
+    float Kw;                   // 315 / (64 pi h^9)
+    float Kg;                   // -45 / (pi h^6)
+    float Kl;                   // 45 / (pi h^6)
+    float rho0, eos_k, dt;
+    float gx, gy, gz;
+    float alpha, beta, eta_h2;  // eta_h2 = eta*h*h
+    float one_plus_e;           // 1 + restitution
+    double wall_off, wall_lim;
+    int nwalls;
+    float wn[kMaxWalls][3];     // wall normal (as given)
+    float wc[kMaxWalls][3];     // wall centre
+    float wu[kMaxWalls][3];     // normalize(normal), computed on the host with IEEE float ops
+    int domain_fixed;
+    float dom_lo[3], dom_hi[3];
+    int periodic[3];
+    long long max_cells;
+    float cell;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// small helpers
+
+__device__ __forceinline__ unsigned int f2ord(float f) {
+    unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned int u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// Cell coordinate along one axis.  Same expression as SphUtils.cpp:38-40, floor((p - min) / cell), in
+// IEEE float (no FMA, true division), then clamped to the grid so that strays stay adjacent to their
+// neighbours.  Bit-exact against the CPU grid build the tests use.
+__device__ __forceinline__ int grid_coord(float x, float origin, float cell, int dim) {
+    float f = floorf(__fdiv_rn(__fsub_rn(x, origin), cell));
+    if (!(f >= 0.0f)) return 0;
+    if (f >= (float)dim) return dim - 1;
+    return (int)f;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K0: bounding box (SphUtils.cpp:11-23).  Grid-stride, warp shuffle, block reduce, then atomics that
+// are skipped when they cannot improve the global value.
+
+__device__ __forceinline__ void bbox_block_commit(float lo[3], float hi[3], BBoxAcc* acc) {
+    __shared__ float s_lo[3][32];
+    __shared__ float s_hi[3][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+        if (lane == 0) { s_lo[a][warp] = lo[a]; s_hi[a][warp] = hi[a]; }
+    }
+    __syncthreads();
+    if (warp == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            float l = lane < nwarp ? s_lo[a][lane] : INFINITY;
+            float h = lane < nwarp ? s_hi[a][lane] : -INFINITY;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+                h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+            }
+            if (lane == 0) {
+                unsigned int ul = f2ord(l), uh = f2ord(h);
+                if (l <= h) { // at least one finite sample
+                    if (ul < *((volatile unsigned int*)&acc->lo[a])) atomicMin(&acc->lo[a], ul);
+                    if (uh > *((volatile unsigned int*)&acc->hi[a])) atomicMax(&acc->hi[a], uh);
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_bbox_reset(BBoxAcc* acc) {
+    if (threadIdx.x < 3) {
+        acc->lo[threadIdx.x] = f2ord(INFINITY);
+        acc->hi[threadIdx.x] = f2ord(-INFINITY);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_bbox(const float4* __restrict__ posm, int n, BBoxAcc* acc) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float4 p = ldg4(posm + i);
+        // fminf/fmaxf drop NaNs, like the reference's `if (x < min)` comparisons
+        lo[0] = fminf(lo[0], p.x); hi[0] = fmaxf(hi[0], p.x);
+        lo[1] = fminf(lo[1], p.y); hi[1] = fmaxf(hi[1], p.y);
+        lo[2] = fminf(lo[2], p.z); hi[2] = fmaxf(hi[2], p.z);
+    }
+    bbox_block_commit(lo, hi, acc);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Grid description from the bounding box (SphUtils.cpp:25-27: n = (int)ceil(extent/cell) + 1) or from
+// the fixed domain; then clear the cell counters [0, ncell].  Every thread derives the same dims;
+// thread 0 of block 0 publishes them.  The tests check the dims against a CPU restatement of the same rule.
+
+__device__ __forceinline__ void derive_grid(const Consts& c, const BBoxAcc* acc, GridDesc& g) {
+    float lo[3], hi[3];
+    if (c.domain_fixed) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) { lo[a] = c.dom_lo[a]; hi[a] = c.dom_hi[a]; }
+    } else {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            lo[a] = ord2f(acc->lo[a]);
+            hi[a] = ord2f(acc->hi[a]);
+            if (!(lo[a] <= hi[a])) { lo[a] = 0.0f; hi[a] = 0.0f; } // no finite particle
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        g.origin[a] = lo[a];
+        g.cell[a] = c.cell;
+        float ext = ceilf(__fdiv_rn(__fsub_rn(hi[a], lo[a]), c.cell));
+        int d = (ext < 1048575.0f) ? (int)ext + 1 : 1048576; // also catches inf/NaN extents
+        g.dims[a] = d < 1 ? 1 : d;
+    }
+    while ((long long)g.dims[0] * g.dims[1] * g.dims[2] > c.max_cells) {
+        int a = 0;
+        if (g.dims[1] > g.dims[a]) a = 1;
+        if (g.dims[2] > g.dims[a]) a = 2;
+        if (g.dims[a] == 1) break;
+        g.dims[a] = (g.dims[a] + 1) / 2;
+    }
+    g.ncell = g.dims[0] * g.dims[1] * g.dims[2];
+    g.stencil = (c.cell >= c.h2) ? 1 : 2;
+    g.pad = 0;
+}
+
+__global__ void __launch_bounds__(256) k_grid_setup(Consts c, const BBoxAcc* acc, GridDesc* out, int* __restrict__ cell_count) {
+    GridDesc g;
+    derive_grid(c, acc, g);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *out = g;
+    const int total = g.ncell + 1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) cell_count[i] = 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K1: cell key + histogram.  slot = arrival rank inside the cell (not deterministic; k_rank_gather
+// replaces it by the stable rank).  Also re-arms the bbox accumulator for this step's force kernel.
+
+__device__ __forceinline__ int cell_key(const GridDesc& g, float x, float y, float z, int& cx, int& cy, int& cz) {
+    cx = grid_coord(x, g.origin[0], g.cell[0], g.dims[0]);
+    cy = grid_coord(y, g.origin[1], g.cell[1], g.dims[1]);
+    cz = grid_coord(z, g.origin[2], g.cell[2], g.dims[2]);
+    return cx + g.dims[0] * (cy + g.dims[1] * cz);
+}
+
+__global__ void __launch_bounds__(256) k_key_hist(const GridDesc* __restrict__ gd, const float4* __restrict__ posm, int n,
+                                                  int* __restrict__ key, int* __restrict__ slot, int* __restrict__ cell_count,
+                                                  BBoxAcc* acc, int rearm_bbox) {
+    const GridDesc g = *gd;
+    if (rearm_bbox && blockIdx.x == 0 && threadIdx.x < 3) {
+        acc->lo[threadIdx.x] = f2ord(INFINITY);
+        acc->hi[threadIdx.x] = f2ord(-INFINITY);
+    }
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 p = ldg4(posm + i);
+    int cx, cy, cz;
+    int k = cell_key(g, p.x, p.y, p.z, cx, cy, cz);
+    key[i] = k;
+    slot[i] = atomicAdd(cell_count + k, 1);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K2: exclusive scan of the cell counters, in place (count -> cell_start), three passes sized by the
+// device-side ncell (the host only knows the capacity).  Tile = 2048 ints per block of 256 threads.
+
+constexpr int kScanThreads = 256;
+constexpr int kScanPerThread = 8;
+constexpr int kScanTile = kScanThreads * kScanPerThread;
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total) {
+    // returns the exclusive prefix of v over the block (kScanThreads threads); *total = block sum
+    __shared__ int s_warp[kScanThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < kScanThreads / 32 ? s_warp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < kScanThreads / 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        if (lane < kScanThreads / 32) s_warp[lane] = w; // inclusive over warps
+    }
+    __syncthreads();
+    int warp_off = warp ? s_warp[warp - 1] : 0;
+    *total = s_warp[kScanThreads / 32 - 1];
+    __syncthreads(); // s_warp is reused by the next call
+    return warp_off + inc - v;
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_reduce(const GridDesc* __restrict__ gd, const int* __restrict__ data, int* __restrict__ block_sums) {
+    const int total = gd->ncell + 1;
+    const int base = blockIdx.x * kScanTile;
+    if (base >= total) return;
+    int s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; k++) {
+        int i = base + k * kScanThreads + threadIdx.x;
+        if (i < total) s += data[i];
+    }
+    int tot;
+    block_exclusive_scan(s, &tot);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+// one block: exclusive scan of the per-tile sums, in place
+__global__ void __launch_bounds__(kScanThreads) k_scan_top(const GridDesc* __restrict__ gd, int* __restrict__ block_sums) {
+    const int ntile = (gd->ncell + 1 + kScanTile - 1) / kScanTile;
+    int carry = 0;
+    for (int base = 0; base < ntile; base += kScanThreads) {
+        int i = base + threadIdx.x;
+        int v = i < ntile ? block_sums[i] : 0;
+        int tot;
+        int ex = block_exclusive_scan(v, &tot);
+        if (i < ntile) block_sums[i] = carry + ex;
+        carry += tot;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_apply(const GridDesc* __restrict__ gd, int* __restrict__ data, const int* __restrict__ block_sums) {
+    const int total = gd->ncell + 1;
+    const int base = blockIdx.x * kScanTile;
+    if (base >= total) return;
+    // each thread owns kScanPerThread consecutive ints
+    int v[kScanPerThread];
+    int s = 0;
+    const int first = base + threadIdx.x * kScanPerThread;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; k++) {
+        v[k] = (first + k < total) ? data[first + k] : 0;
+        s += v[k];
+    }
+    int tot;
+    int ex = block_exclusive_scan(s, &tot) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; k++) {
+        if (first + k < total) data[first + k] = ex;
+        ex += v[k];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K3: scatter (original id, current index) pairs into their cell segment in arrival order, then
+// k_rank_gather replaces the arrival order by the STABLE order (ascending original id inside a cell,
+// i.e. exactly what a CPU stable counting sort of the uploaded order produces) and moves the state.
+
+__global__ void __launch_bounds__(256) k_scatter(const int* __restrict__ key, const int* __restrict__ slot, const int* __restrict__ oid,
+                                                 const int* __restrict__ cell_start, int2* __restrict__ pairs, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    pairs[cell_start[key[i]] + slot[i]] = make_int2(oid[i], i);
+}
+
+template <bool kCarryAll>
+__global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pairs, const int* __restrict__ key, const int* __restrict__ cell_start,
+                                                     const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
+                                                     const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
+                                                     float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                     float4* __restrict__ aux_out, float4* __restrict__ acc_out,
+                                                     int* __restrict__ oid_out, int n) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int2 me = pairs[p];
+    const int k = key[me.y];
+    const int b = cell_start[k], e = cell_start[k + 1];
+    int rank = 0;
+    for (int q = b; q < e; q++) rank += (pairs[q].x < me.x);
+    const int dst = b + rank;
+    posm_out[dst] = ldg4(posm_in + me.y);
+    vel_out[dst] = ldg4(vel_in + me.y);
+    if (kCarryAll) {
+        aux_out[dst] = ldg4(aux_in + me.y);
+        acc_out[dst] = ldg4(acc_in + me.y);
+    }
+    oid_out[dst] = me.x;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// SPH kernel shapes (SphUtils.cpp:55-95).  The reference evaluates the polynomial in double and rounds
+// once; here everything is FP32 with the constant factor applied after the neighbour sum
+// (tolerance-checked: <= 1e-5 relative on density and acceleration, tests/test_gpu_parity.py).
+
+// (h^2 - q^2)^3 with q^2 = d2/h^2, zero outside the support (q <= h  <=>  d2 <= h^4)
+__device__ __forceinline__ float w_shape(const Consts& c, float d2) {
+    float t = fmaxf(fmaf(-d2, c.inv_h2, c.h2), 0.0f);
+    return t * t * t;
+}
+
+// Visits every candidate run [jb, je) of sorted slots in the (2S+1)^2 rows around cell (cx,cy,cz).
+// Along x the 2S+1 cells of a row are contiguous in the sorted arrays, so a row is one run.
+template <class F>
+__device__ __forceinline__ void for_each_run(const GridDesc& g, const int* __restrict__ cell_start, int cx, int cy, int cz, F&& f) {
+    const int S = g.stencil;
+    const int x0 = max(cx - S, 0), x1 = min(cx + S, g.dims[0] - 1);
+    const int z0 = max(cz - S, 0), z1 = min(cz + S, g.dims[2] - 1);
+    const int y0 = max(cy - S, 0), y1 = min(cy + S, g.dims[1] - 1);
+    for (int z = z0; z <= z1; z++) {
+        for (int y = y0; y <= y1; y++) {
+            const int row = g.dims[0] * (y + g.dims[1] * z);
+            const int jb = __ldg(cell_start + row + x0);
+            const int je = __ldg(cell_start + row + x1 + 1);
+            f(jb, je);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K4: density + equation of state (SphUtils.cpp:100-149).  One thread per sorted particle.
+// aux = (rho, P, sqrt|P/rho|, 1/rho): the last two are precomputed for the force kernel
+// (SphUtils.cpp:223 evaluates sqrt|P/rho| per pair).
+
+__device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
+    float rho = sum * c.Kw;
+    if (rho < c.rho0) rho = c.rho0;                 // SphUtils.cpp:141-142 (clamp UP)
+    float P = __fmul_rn(c.eos_k, __fsub_rn(rho, c.rho0)); // :144
+    float inv = __frcp_rn(rho);
+    return make_float4(rho, P, sqrtf(fabsf(__fdiv_rn(P, rho))), inv);
+}
+
+__global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                 const float4* __restrict__ posm, float4* __restrict__ aux, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const GridDesc g = *gd;
+    const float4 pi = ldg4(posm + i);
+    int cx, cy, cz;
+    cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
+    float sum = 0.0f;
+    for_each_run(g, cell_start, cx, cy, cz, [&](int jb, int je) {
+#pragma unroll 4
+        for (int j = jb; j < je; j++) {
+            const float4 pj = ldg4(posm + j);
+            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+            float w = w_shape(c, d2);
+            w = (j == i) ? 0.0f : w; // the self term is excluded by index (SphUtils.cpp:132)
+            sum = fmaf(pj.w, w, sum);
+        }
+    });
+    aux[i] = finish_density(c, sum);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K5: pressure + artificial-viscosity pair force (SphUtils.cpp:181-239), gravity (:295-304), and --
+// fused -- symplectic Euler (:321-335) and wall collision (:343-372).
+
+// One pair (i <- j), in range (d2 < R2), accumulates the direction-weighted scalar; the factor
+// Kg = -45/(pi h^6) is applied once after the sum.
+__device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, float dz, float d2, const float4& vi, const float4& ai,
+                                           float mj, const float4& vj, const float4& aj, float& ax, float& ay, float& az) {
+    const float vdotr = fmaf(vi.x - vj.x, dx, fmaf(vi.y - vj.y, dy, (vi.z - vj.z) * dz)); // :220
+    const float rinv = rsqrtf(d2);
+    const float r = d2 * rinv;
+    const float s = fmaf(-r, c.inv_h, c.h); // h - q, q = r/h              (:70-74)
+    float visc = 0.0f;
+    if (vdotr < 0.0f) {                                                                  // :222-227
+        const float cbar = 0.5f * (ai.z + aj.z);
+        const float mu = __fdividef(c.h * vdotr, d2 + c.eta_h2);
+        visc = __fdividef(2.0f * mu * fmaf(c.beta, mu, -c.alpha * cbar), ai.x + aj.x);
+    }
+    // :228  -(m_j) * (pi + (P_i + P_j) / (2 rho_j rho_i)); ai.w, aj.w = 1/rho
+    const float t = -mj * fmaf(0.5f * (ai.y + aj.y), ai.w * aj.w, visc);
+    const float wgt = t * s * s * rinv; // times (x_i - x_j) = temp * |gradW| * normalize(i - j) / Kg
+    ax = fmaf(wgt, dx, ax);
+    ay = fmaf(wgt, dy, ay);
+    az = fmaf(wgt, dz, az);
+}
+
+// SphUtils.cpp:326-328 with the reference's rounding (mul then add, no FMA): bit-exact given equal accel
+__device__ __forceinline__ void integrate(const Consts& c, float4& p, float4& v, float ax, float ay, float az) {
+    v.x = __fadd_rn(v.x, __fmul_rn(c.dt, ax));
+    v.y = __fadd_rn(v.y, __fmul_rn(c.dt, ay));
+    v.z = __fadd_rn(v.z, __fmul_rn(c.dt, az));
+    p.x = __fadd_rn(p.x, __fmul_rn(c.dt, v.x));
+    p.y = __fadd_rn(p.y, __fmul_rn(c.dt, v.y));
+    p.z = __fadd_rn(p.z, __fmul_rn(c.dt, v.z));
+}
+
+// SphUtils.cpp:346-372, walls in vector order, each seeing the previous one's correction; the hit test
+// runs in double like the reference's double literals.  Bit-exact given equal inputs.
+__device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4& v) {
+    for (int w = 0; w < c.nwalls; w++) {
+        const float nx = c.wn[w][0], ny = c.wn[w][1], nz = c.wn[w][2];
+        float d = __fadd_rn(__fadd_rn(__fmul_rn(nx, __fsub_rn(p.x, c.wc[w][0])), __fmul_rn(ny, __fsub_rn(p.y, c.wc[w][1]))),
+                            __fmul_rn(nz, __fsub_rn(p.z, c.wc[w][2])));
+        if ((double)d + c.wall_off <= c.wall_lim || (double)d - c.wall_off <= c.wall_lim) {
+            const float ndv = __fadd_rn(__fadd_rn(__fmul_rn(nx, v.x), __fmul_rn(ny, v.y)), __fmul_rn(nz, v.z));
+            const float k = __fmul_rn(c.one_plus_e, ndv);
+            if (d < 0.0f) d = -d;
+            p.x = __fadd_rn(p.x, __fmul_rn(d, nx));
+            p.y = __fadd_rn(p.y, __fmul_rn(d, ny));
+            p.z = __fadd_rn(p.z, __fmul_rn(d, nz));
+            v.x = __fadd_rn(v.x, -__fmul_rn(c.wu[w][0], k));
+            v.y = __fadd_rn(v.y, -__fmul_rn(c.wu[w][1], k));
+            v.z = __fadd_rn(v.z, -__fmul_rn(c.wu[w][2], k));
+        }
+    }
+}
+
+// kFused: also integrate + collide and write the new state to the other buffer (ping-pong: every
+//         thread reads only old buffers, so the fusion is race-free).
+// kBBox:  also fold the new positions into the bounding box for the next step's grid.
+// kAccel: store the acceleration (parity, viewers).
+template <bool kFused, bool kBBox, bool kAccel>
+__global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                               const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
+                                               float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                               BBoxAcc* bbox, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (i < n) {
+        const GridDesc g = *gd;
+        const float4 pi = ldg4(posm + i);
+        const float4 vi = ldg4(vel + i);
+        const float4 ai = ldg4(aux + i);
+        int cx, cy, cz;
+        cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
+        float ax = 0.0f, ay = 0.0f, az = 0.0f;
+        for_each_run(g, cell_start, cx, cy, cz, [&](int jb, int je) {
+            for (int j = jb; j < je; j++) {
+                const float4 pj = ldg4(posm + j);
+                const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                // q < h  <=>  d2 < h^4; NaN-safe form keeps the reference's NaN for coincident points
+                if (!(d2 >= c.R2) && j != i) {
+                    const float4 vj = ldg4(vel + j);
+                    const float4 aj = ldg4(aux + j);
+                    pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, vj, aj, ax, ay, az);
+                }
+            }
+        });
+        ax = fmaf(c.Kg, ax, c.gx);
+        ay = fmaf(c.Kg, ay, c.gy);
+        az = fmaf(c.Kg, az, c.gz);
+        if (kAccel) accel[i] = make_float4(ax, ay, az, 0.0f);
+        if (kFused) {
+            float4 p = pi, v = vi;
+            integrate(c, p, v, ax, ay, az);
+            collide_walls(c, p, v);
+            posm_out[i] = p;
+            vel_out[i] = v;
+            if (kBBox) {
+                lo[0] = hi[0] = p.x; lo[1] = hi[1] = p.y; lo[2] = hi[2] = p.z;
+#pragma unroll
+                for (int a = 0; a < 3; a++)
+                    if (!(lo[a] == lo[a])) { lo[a] = INFINITY; hi[a] = -INFINITY; } // NaN: ignored like the reference's compares
+            }
+        }
+    }
+    if (kFused && kBBox) bbox_block_commit(lo, hi, bbox);
+}
+
+// Phase kernels for the method-by-method API (update_posvel, collision), in place.
+__global__ void __launch_bounds__(256) k_posvel(Consts c, float4* __restrict__ posm, float4* __restrict__ vel, const float4* __restrict__ accel, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 p = posm[i], v = vel[i];
+    const float4 a = accel[i];
+    integrate(c, p, v, a.x, a.y, a.z);
+    posm[i] = p;
+    vel[i] = v;
+}
+
+__global__ void __launch_bounds__(256) k_collision(Consts c, float4* __restrict__ posm, float4* __restrict__ vel, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 p = posm[i], v = vel[i];
+    collide_walls(c, p, v);
+    posm[i] = p;
+    vel[i] = v;
+}
+
+// kernel_function / grad_kernel / lap_kernel for explicit point pairs, same device math as above
+__global__ void __launch_bounds__(256) k_eval_kernels(Consts c, const float* __restrict__ xi, const float* __restrict__ xj, int count,
+                                                      float* __restrict__ w, float* __restrict__ grad, float* __restrict__ lap) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const float dx = xi[3 * t] - xj[3 * t], dy = xi[3 * t + 1] - xj[3 * t + 1], dz = xi[3 * t + 2] - xj[3 * t + 2];
+    const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+    if (w) w[t] = c.Kw * w_shape(c, d2);
+    const float rinv = rsqrtf(d2);
+    const float r = d2 * rinv;
+    const float s = fmaf(-r, c.inv_h, c.h);
+    const bool in = !(d2 >= c.R2);
+    if (grad) {
+        const float m = in ? c.Kg * s * s : 0.0f;
+        grad[3 * t] = dx * rinv * m;      // normalize(i - j) * result; NaN at r = 0 like the reference
+        grad[3 * t + 1] = dy * rinv * m;
+        grad[3 * t + 2] = dz * rinv * m;
+    }
+    if (lap) lap[t] = (in && d2 > 0.0f) ? c.Kl * s : (in ? c.Kl * c.h : 0.0f);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// AoS (the reference's 52-byte Particle) <-> SoA.  Records are staged through shared memory so that
+// global traffic is fully coalesced 4-byte words regardless of the odd record size.
+
+constexpr int kAosThreads = 256;
+
+// word offsets inside a record (SPH/Particle.hpp:42-50)
+constexpr int kOffPos = 0, kOffVel = 3, kOffAcc = 6, kOffMass = 9, kOffRho = 10, kOffP = 11;
+
+__global__ void __launch_bounds__(kAosThreads) k_aos_to_soa(const float* __restrict__ aos, int stride_w, int n, float4* __restrict__ posm,
+                                                            float4* __restrict__ vel, float4* __restrict__ aux, float4* __restrict__ accel,
+                                                            int* __restrict__ oid) {
+    extern __shared__ float s_rec[];
+    const int base = blockIdx.x * kAosThreads;
+    const int cnt = min(kAosThreads, n - base);
+    const long long wbase = (long long)base * stride_w;
+    for (int w = threadIdx.x; w < cnt * stride_w; w += kAosThreads) s_rec[w] = aos[wbase + w];
+    __syncthreads();
+    if (threadIdx.x >= cnt) return;
+    const float* r = s_rec + threadIdx.x * stride_w;
+    const int i = base + threadIdx.x;
+    posm[i] = make_float4(r[kOffPos], r[kOffPos + 1], r[kOffPos + 2], r[kOffMass]);
+    vel[i] = make_float4(r[kOffVel], r[kOffVel + 1], r[kOffVel + 2], 0.0f);
+    const float rho = r[kOffRho], P = r[kOffP];
+    aux[i] = make_float4(rho, P, sqrtf(fabsf(__fdiv_rn(P, rho))), __frcp_rn(rho));
+    accel[i] = make_float4(r[kOffAcc], r[kOffAcc + 1], r[kOffAcc + 2], 0.0f);
+    oid[i] = i;
+}
+
+// Sorted SoA -> AoS in ORIGINAL order.  inv[o] = sorted slot of original particle o.
+__global__ void __launch_bounds__(256) k_invert_perm(const int* __restrict__ oid, int* __restrict__ inv, int n) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) inv[oid[p]] = p;
+}
+
+__global__ void __launch_bounds__(kAosThreads) k_soa_to_aos(float* __restrict__ aos, int stride_w, int n, const int* __restrict__ inv,
+                                                            const float4* __restrict__ posm, const float4* __restrict__ vel,
+                                                            const float4* __restrict__ aux, const float4* __restrict__ accel, unsigned mask) {
+    extern __shared__ float s_rec[];
+    const int base = blockIdx.x * kAosThreads;
+    const int cnt = min(kAosThreads, n - base);
+    const long long wbase = (long long)base * stride_w;
+    // read-modify-write so that fields outside the mask (and thermal, padding) keep their bytes
+    for (int w = threadIdx.x; w < cnt * stride_w; w += kAosThreads) s_rec[w] = aos[wbase + w];
+    __syncthreads();
+    if (threadIdx.x < cnt) {
+        float* r = s_rec + threadIdx.x * stride_w;
+        const int p = inv[base + threadIdx.x];
+        if (mask & 1u) { const float4 q = posm[p]; r[kOffPos] = q.x; r[kOffPos + 1] = q.y; r[kOffPos + 2] = q.z; }
+        if (mask & 2u) { const float4 q = vel[p]; r[kOffVel] = q.x; r[kOffVel + 1] = q.y; r[kOffVel + 2] = q.z; }
+        if (mask & 4u) { const float4 q = accel[p]; r[kOffAcc] = q.x; r[kOffAcc + 1] = q.y; r[kOffAcc + 2] = q.z; }
+        if (mask & 8u) { const float4 q = aux[p]; r[kOffRho] = q.x; r[kOffP] = q.y; }
+    }
+    __syncthreads();
+    for (int w = threadIdx.x; w < cnt * stride_w; w += kAosThreads) aos[wbase + w] = s_rec[w];
+}
+
+// grid diagnostics for the bit-exact grid test: cell coordinates in ORIGINAL order
+__global__ void __launch_bounds__(256) k_cells_xyz(const GridDesc* __restrict__ gd, const float4* __restrict__ posm, const int* __restrict__ oid,
+                                                   int* __restrict__ xyz, int n) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const GridDesc g = *gd;
+    const float4 q = posm[p];
+    int cx, cy, cz;
+    cell_key(g, q.x, q.y, q.z, cx, cy, cz);
+    const int o = oid[p];
+    xyz[3 * o] = cx; xyz[3 * o + 1] = cy; xyz[3 * o + 2] = cz;
+}
+
+// device-to-device upload helper: ids default to 0..n-1
+__global__ void __launch_bounds__(256) k_fill_iota(int* __restrict__ ids, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) ids[i] = i;
+}
+
+} // namespace sphb

@@ -1,0 +1,632 @@
+// Host side of libsphb200.so: the C ABI declared in include/sphb200.h over the kernels of
+// sphb_device.cuh.  One engine = one GPU = one stream.  No CPU compute path exists: every entry
+// point either launches CUDA work or fails with an error code.
+#include "../../include/sphb200.h"
+#include "sphb_device.cuh"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+using namespace sphb;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CK(call)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t _e = (call);                                                                              \
+        if (_e != cudaSuccess)                                                                                \
+            return fail(SPHB_ERR_CUDA, "%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(_e)); \
+    } while (0)
+
+inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0; // elements
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc((void**)&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+} // namespace
+
+struct sphb_engine {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    sphb_params params;
+    Consts c;
+    size_t n = 0;
+    int cur = 0; // which ping-pong buffer holds the current state
+
+    DevBuf<float4> posm[2], vel[2], aux[2], accel[2];
+    DevBuf<int> oid[2];
+    DevBuf<int> key, slot, inv;
+    DevBuf<int2> pairs;
+    DevBuf<int> cell_start; // max_cells + 1 (+ slack)
+    DevBuf<int> block_sums;
+    DevBuf<float> aos;      // staging for host AoS records
+    DevBuf<float> scratch;  // eval_kernels, cells download
+    GridDesc* d_grid = nullptr;
+    BBoxAcc* d_bbox = nullptr;
+    long long max_cells = 0;
+
+    bool have_state = false;
+    bool grid_valid = false; // cell_start / sorted order correspond to the current positions
+    bool bbox_valid = false; // d_bbox holds the bbox of the current positions
+    bool aos_valid = false;  // staging holds the bytes of the last AoS upload
+    size_t aos_stride_w = 13;
+
+    bool timing = false;
+    static constexpr int kMaxTimed = 256;     // steps whose phase events are kept since timing was enabled
+    cudaEvent_t* ev = nullptr;                // [kMaxTimed][4]
+    int timed_steps = 0;
+    uint64_t launches = 0;
+};
+
+namespace {
+
+#define LAUNCH(e, kernel, grid, block, smem, ...)                                   \
+    do {                                                                            \
+        kernel<<<(grid), (block), (smem), (e)->stream>>>(__VA_ARGS__);              \
+        (e)->launches++;                                                            \
+    } while (0)
+
+int use_device(sphb_engine* e) {
+    CK(cudaSetDevice(e->device));
+    return SPHB_OK;
+}
+
+void build_consts(sphb_engine* e) {
+    const sphb_params& p = e->params;
+    Consts& c = e->c;
+    memset(&c, 0, sizeof c);
+    const float pi_f = (float)3.14159265358979323846264338327950288; // glm::pi<float>()
+    c.h = p.h;
+    c.h2 = p.h * p.h;
+    c.inv_h = 1.0f / p.h;
+    c.inv_h2 = 1.0f / c.h2;
+    c.R2 = c.h2 * c.h2;
+    // same double expressions as SphUtils.cpp:61,74,91, rounded once
+    c.Kw = (float)(315.0 / ((double)(64 * pi_f) * pow((double)p.h, 9)));
+    c.Kg = (float)(-45.0 / ((double)pi_f * pow((double)p.h, 6)));
+    c.Kl = (float)(45.0 / ((double)pi_f * pow((double)p.h, 6)));
+    c.rho0 = p.rho0;
+    c.eos_k = p.eos_k;
+    c.dt = p.dt;
+    c.gx = p.gravity[0]; c.gy = p.gravity[1]; c.gz = p.gravity[2];
+    c.alpha = p.visc_alpha;
+    c.beta = p.visc_beta;
+    c.eta_h2 = p.visc_eta * p.h * p.h;
+    c.one_plus_e = 1.0f + p.restitution;
+    c.wall_off = p.wall_test_off;
+    c.wall_lim = p.wall_test_lim;
+    c.domain_fixed = p.domain_mode == SPHB_DOMAIN_FIXED;
+    for (int a = 0; a < 3; a++) {
+        c.dom_lo[a] = p.domain_lo[a];
+        c.dom_hi[a] = p.domain_hi[a];
+        c.periodic[a] = p.periodic[a];
+    }
+    c.cell = p.cell_size > 0.0f ? p.cell_size : c.h2;
+}
+
+int ensure_capacity(sphb_engine* e, size_t n) {
+    const size_t want = n ? n : 1;
+    for (int b = 0; b < 2; b++) {
+        CK(e->posm[b].reserve(want));
+        CK(e->vel[b].reserve(want));
+        CK(e->aux[b].reserve(want));
+        CK(e->accel[b].reserve(want));
+        CK(e->oid[b].reserve(want));
+    }
+    CK(e->key.reserve(want));
+    CK(e->slot.reserve(want));
+    CK(e->inv.reserve(want));
+    CK(e->pairs.reserve(want));
+    long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)(2 * want + 65536);
+    if (mc > (1ll << 30)) mc = 1ll << 30;
+    if (mc > e->max_cells) {
+        CK(e->cell_start.reserve((size_t)mc + 2));
+        CK(e->block_sums.reserve((size_t)cdiv(mc + 2, kScanTile) + 1));
+        e->max_cells = mc;
+    }
+    e->c.max_cells = e->max_cells;
+    return SPHB_OK;
+}
+
+// bbox of the current positions -> d_bbox
+int run_bbox(sphb_engine* e) {
+    const int n = (int)e->n;
+    LAUNCH(e, k_bbox_reset, 1, 32, 0, e->d_bbox);
+    int blocks = cdiv(n, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    LAUNCH(e, k_bbox, blocks, 256, 0, e->posm[e->cur].p, n, e->d_bbox);
+    e->bbox_valid = true;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+// K0..K3: grid description, keys, stable counting sort, reorder into the other ping-pong buffer.
+int run_sort(sphb_engine* e, bool carry_all) {
+    const int n = (int)e->n;
+    if (!e->c.domain_fixed && !e->bbox_valid) {
+        int rc = run_bbox(e);
+        if (rc) return rc;
+    }
+    const int cur = e->cur, nxt = cur ^ 1;
+    const int ntile_cap = cdiv(e->max_cells + 1, kScanTile);
+    int setup_blocks = cdiv(e->max_cells + 1, 256 * 8);
+    if (setup_blocks > 148 * 8) setup_blocks = 148 * 8;
+    LAUNCH(e, k_grid_setup, setup_blocks, 256, 0, e->c, e->d_bbox, e->d_grid, e->cell_start.p);
+    const int pb = cdiv(n, 256);
+    LAUNCH(e, k_key_hist, pb, 256, 0, e->d_grid, e->posm[cur].p, n, e->key.p, e->slot.p, e->cell_start.p, e->d_bbox,
+           e->c.domain_fixed ? 0 : 1);
+    LAUNCH(e, k_scan_reduce, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
+    LAUNCH(e, k_scan_top, 1, kScanThreads, 0, e->d_grid, e->block_sums.p);
+    LAUNCH(e, k_scan_apply, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
+    LAUNCH(e, k_scatter, pb, 256, 0, e->key.p, e->slot.p, e->oid[cur].p, e->cell_start.p, e->pairs.p, n);
+    if (carry_all)
+        LAUNCH(e, k_rank_gather<true>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n);
+    else
+        LAUNCH(e, k_rank_gather<false>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n);
+    CK(cudaGetLastError());
+    e->cur = nxt;
+    e->grid_valid = true;
+    e->bbox_valid = false; // k_key_hist re-armed the accumulator
+    return SPHB_OK;
+}
+
+int run_density(sphb_engine* e) {
+    const int n = (int)e->n;
+    LAUNCH(e, k_density, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->aux[e->cur].p, n);
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int check_ready(sphb_engine* e) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (!e->have_state) return fail(SPHB_ERR_STATE, "no particles uploaded");
+    return use_device(e);
+}
+
+} // namespace
+
+extern "C" {
+
+void sphb_default_params(sphb_params* p) {
+    if (!p) return;
+    memset(p, 0, sizeof *p);
+    p->h = 0.45f;      // main.cpp:34
+    p->rho0 = 10.0f;   // main.cpp:36
+    p->c = 100.0f;     // main.cpp:38
+    p->dt = 0.033f;    // main.cpp:30
+    p->eps = 0.01f;    // main.cpp:40
+    p->eos_k = 100.0f; // SphUtils.cpp:144
+    p->gravity[0] = 0.0f; p->gravity[1] = -1.0f; p->gravity[2] = 0.0f; // SphUtils.cpp:298
+    p->visc_alpha = 0.1f;  // SphUtils.cpp:226
+    p->visc_beta = 0.2f;   // SphUtils.cpp:226
+    p->visc_eta = 0.01f;   // SphUtils.cpp:225
+    p->restitution = 0.0f; // SphUtils.cpp:352
+    p->cell_size = 0.0f;
+    p->wall_test_off = 0.001; // SphUtils.cpp:349
+    p->wall_test_lim = 0.01;
+    p->domain_mode = SPHB_DOMAIN_BBOX;
+    p->max_cells = 0;
+    p->write_accel = 1;
+}
+
+const char* sphb_last_error(void) { return g_err; }
+const char* sphb_version(void) { return "sphb200 0.1 (sm_100a)"; }
+size_t sphb_params_size(void) { return sizeof(sphb_params); }
+
+int sphb_create(const sphb_params* p, int device, sphb_engine** out) {
+    if (!p || !out) return fail(SPHB_ERR_INVALID, "null argument");
+    if (!(p->h > 0.0f) || !(p->rho0 > 0.0f)) return fail(SPHB_ERR_INVALID, "h and rho0 must be positive");
+    const float R = p->h * p->h;
+    if (p->cell_size != 0.0f && !(p->cell_size >= 0.5f * R)) return fail(SPHB_ERR_INVALID, "cell_size must be 0 or >= h*h/2");
+    if (p->domain_mode != SPHB_DOMAIN_BBOX && p->domain_mode != SPHB_DOMAIN_FIXED) return fail(SPHB_ERR_INVALID, "bad domain_mode");
+    if (p->periodic[0] || p->periodic[1] || p->periodic[2]) return fail(SPHB_ERR_INVALID, "periodic axes are not implemented yet");
+    if (p->domain_mode == SPHB_DOMAIN_FIXED)
+        for (int a = 0; a < 3; a++)
+            if (!(p->domain_hi[a] >= p->domain_lo[a])) return fail(SPHB_ERR_INVALID, "fixed domain needs hi >= lo");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(SPHB_ERR_INVALID, "device %d out of range (%d visible)", device, ndev);
+    sphb_engine* e = new (std::nothrow) sphb_engine();
+    if (!e) return fail(SPHB_ERR_INVALID, "out of host memory");
+    e->device = device;
+    e->params = *p;
+    build_consts(e);
+    cudaError_t err = cudaSetDevice(device);
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_grid, sizeof(GridDesc));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_bbox, sizeof(BBoxAcc));
+    if (err != cudaSuccess) {
+        sphb_destroy(e);
+        return fail(SPHB_ERR_CUDA, "engine setup failed: %s", cudaGetErrorString(err));
+    }
+    *out = e;
+    g_err[0] = 0;
+    return SPHB_OK;
+}
+
+void sphb_destroy(sphb_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    for (int b = 0; b < 2; b++) {
+        e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
+    }
+    e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release();
+    e->cell_start.release(); e->block_sums.release(); e->aos.release(); e->scratch.release();
+    if (e->d_grid) cudaFree(e->d_grid);
+    if (e->d_bbox) cudaFree(e->d_bbox);
+    if (e->ev) {
+        for (int i = 0; i < 4 * sphb_engine::kMaxTimed; i++) cudaEventDestroy(e->ev[i]);
+        delete[] e->ev;
+    }
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int sphb_set_walls(sphb_engine* e, const void* walls, size_t count, size_t stride) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (count > SPHB_MAX_WALLS) return fail(SPHB_ERR_CAPACITY, "at most %d walls", SPHB_MAX_WALLS);
+    if (count && (!walls || stride < 24)) return fail(SPHB_ERR_INVALID, "walls need >= 24-byte records");
+    e->c.nwalls = (int)count;
+    for (size_t w = 0; w < count; w++) {
+        float f[6];
+        memcpy(f, (const char*)walls + w * stride, sizeof f);
+        for (int a = 0; a < 3; a++) { e->c.wn[w][a] = f[a]; e->c.wc[w][a] = f[3 + a]; }
+        // glm::normalize(n) = n * (1 / sqrt(dot(n, n))), float ops in this order (SphUtils.cpp:351)
+        volatile float tx = f[0] * f[0], ty = f[1] * f[1], tz = f[2] * f[2];
+        volatile float s = tx + ty;
+        s = s + tz;
+        volatile float inv = 1.0f / sqrtf(s);
+        for (int a = 0; a < 3; a++) e->c.wu[w][a] = f[a] * inv;
+    }
+    return SPHB_OK;
+}
+
+int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stride) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (n && !particles) return fail(SPHB_ERR_INVALID, "null particles");
+    if (stride < 48 || stride % 4 || stride > 128) return fail(SPHB_ERR_INVALID, "stride must be a multiple of 4 in [48, 128]");
+    if (n > 0x7fffff00u) return fail(SPHB_ERR_CAPACITY, "too many particles");
+    int rc = use_device(e);
+    if (rc) return rc;
+    rc = ensure_capacity(e, n);
+    if (rc) return rc;
+    const size_t sw = stride / 4;
+    CK(e->aos.reserve((n ? n : 1) * sw));
+    e->n = n;
+    e->cur = 0;
+    e->aos_stride_w = sw;
+    if (n) {
+        CK(cudaMemcpyAsync(e->aos.p, particles, n * stride, cudaMemcpyHostToDevice, e->stream));
+        LAUNCH(e, k_aos_to_soa, cdiv(n, kAosThreads), kAosThreads, kAosThreads * stride, e->aos.p, (int)sw, (int)n, e->posm[0].p,
+               e->vel[0].p, e->aux[0].p, e->accel[0].p, e->oid[0].p);
+        CK(cudaGetLastError());
+    }
+    e->have_state = true;
+    e->grid_valid = false;
+    e->bbox_valid = false;
+    e->aos_valid = true;
+    return SPHB_OK;
+}
+
+int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, const int32_t* ids, size_t n) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (n && (!posm || !vel)) return fail(SPHB_ERR_INVALID, "null device arrays");
+    if (n > 0x7fffff00u) return fail(SPHB_ERR_CAPACITY, "too many particles");
+    int rc = use_device(e);
+    if (rc) return rc;
+    rc = ensure_capacity(e, n);
+    if (rc) return rc;
+    e->n = n;
+    e->cur = 0;
+    if (n) {
+        CK(cudaMemcpyAsync(e->posm[0].p, posm, n * sizeof(float4), cudaMemcpyDeviceToDevice, e->stream));
+        CK(cudaMemcpyAsync(e->vel[0].p, vel, n * sizeof(float4), cudaMemcpyDeviceToDevice, e->stream));
+        CK(cudaMemsetAsync(e->aux[0].p, 0, n * sizeof(float4), e->stream));
+        CK(cudaMemsetAsync(e->accel[0].p, 0, n * sizeof(float4), e->stream));
+        if (ids) CK(cudaMemcpyAsync(e->oid[0].p, ids, n * sizeof(int), cudaMemcpyDeviceToDevice, e->stream));
+        else LAUNCH(e, k_fill_iota, cdiv(n, 256), 256, 0, e->oid[0].p, (int)n);
+        CK(cudaGetLastError());
+    }
+    e->have_state = true;
+    e->grid_valid = false;
+    e->bbox_valid = false;
+    e->aos_valid = false;
+    return SPHB_OK;
+}
+
+int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (n != e->n) return fail(SPHB_ERR_INVALID, "download of %zu particles but the engine holds %zu", n, e->n);
+    if (n && !particles) return fail(SPHB_ERR_INVALID, "null particles");
+    if (stride < 48 || stride % 4 || stride > 128) return fail(SPHB_ERR_INVALID, "stride must be a multiple of 4 in [48, 128]");
+    if (n == 0) return SPHB_OK;
+    const size_t sw = stride / 4;
+    if (!e->aos_valid || sw != e->aos_stride_w) {
+        // no faithful copy of the host records on the device: fetch them so unmasked fields survive
+        CK(e->aos.reserve(n * sw));
+        CK(cudaMemcpyAsync(e->aos.p, particles, n * stride, cudaMemcpyHostToDevice, e->stream));
+        e->aos_stride_w = sw;
+        e->aos_valid = true;
+    }
+    const int cur = e->cur;
+    LAUNCH(e, k_invert_perm, cdiv(n, 256), 256, 0, e->oid[cur].p, e->inv.p, (int)n);
+    LAUNCH(e, k_soa_to_aos, cdiv(n, kAosThreads), kAosThreads, kAosThreads * stride, e->aos.p, (int)sw, (int)n, e->inv.p, e->posm[cur].p,
+           e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, field_mask);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(particles, e->aos.p, n * stride, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return SPHB_OK;
+}
+
+int sphb_update_cells(sphb_engine* e) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (e->n == 0) return SPHB_OK;
+    return run_sort(e, true);
+}
+
+int sphb_update_density(sphb_engine* e) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (e->n == 0) return SPHB_OK;
+    if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
+    return run_density(e);
+}
+
+int sphb_update_forces(sphb_engine* e) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (e->n == 0) return SPHB_OK;
+    if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
+    const int n = (int)e->n, cur = e->cur;
+    auto kfn = k_force<false, false, true>;
+    LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p,
+           e->aux[cur].p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_update_posvel(sphb_engine* e) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (e->n == 0) return SPHB_OK;
+    const int n = (int)e->n, cur = e->cur;
+    LAUNCH(e, k_posvel, cdiv(n, 256), 256, 0, e->c, e->posm[cur].p, e->vel[cur].p, e->accel[cur].p, n);
+    CK(cudaGetLastError());
+    e->grid_valid = false;
+    e->bbox_valid = false;
+    return SPHB_OK;
+}
+
+int sphb_collision(sphb_engine* e) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (e->n == 0) return SPHB_OK;
+    const int n = (int)e->n, cur = e->cur;
+    LAUNCH(e, k_collision, cdiv(n, 256), 256, 0, e->c, e->posm[cur].p, e->vel[cur].p, n);
+    CK(cudaGetLastError());
+    e->grid_valid = false;
+    e->bbox_valid = false;
+    return SPHB_OK;
+}
+
+int sphb_step(sphb_engine* e, int nsteps) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (nsteps < 0) return fail(SPHB_ERR_INVALID, "nsteps < 0");
+    if (e->n == 0) return SPHB_OK;
+    const int n = (int)e->n;
+    const bool bbox = !e->c.domain_fixed;
+    const bool acc = e->params.write_accel != 0;
+    for (int s = 0; s < nsteps; s++) {
+        const bool timed = e->timing && e->timed_steps < sphb_engine::kMaxTimed;
+        cudaEvent_t* ev = timed ? e->ev + 4 * e->timed_steps : nullptr;
+        if (timed) CK(cudaEventRecord(ev[0], e->stream));
+        // Always re-sort: positions moved.  (First step after an upload of an already valid grid is rare.)
+        if ((rc = run_sort(e, false))) return rc;
+        if (timed) CK(cudaEventRecord(ev[1], e->stream));
+        if ((rc = run_density(e))) return rc;
+        if (timed) CK(cudaEventRecord(ev[2], e->stream));
+        const int cur = e->cur, nxt = cur ^ 1;
+        const int blocks = cdiv(n, 128);
+#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
+        auto kfn = bbox ? (acc ? k_force<true, true, true> : k_force<true, true, false>)
+                        : (acc ? k_force<true, false, true> : k_force<true, false, false>);
+        LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS);
+#undef FORCE_ARGS
+        CK(cudaGetLastError());
+        // the new state (posm, vel, accel) is in nxt; aux (rho, P) and ids stay where they are: copy-free
+        // hand-over by swapping the roles of those two buffers as well.
+        {
+            DevBuf<float4> t = e->aux[cur]; e->aux[cur] = e->aux[nxt]; e->aux[nxt] = t;
+            DevBuf<int> u = e->oid[cur]; e->oid[cur] = e->oid[nxt]; e->oid[nxt] = u;
+        }
+        e->cur = nxt;
+        e->grid_valid = false;
+        e->bbox_valid = bbox;
+        if (timed) {
+            CK(cudaEventRecord(ev[3], e->stream));
+            e->timed_steps++;
+        }
+    }
+    return SPHB_OK;
+}
+
+int sphb_step_aos(sphb_engine* e, void* particles, size_t n, size_t stride, int nsteps, uint32_t field_mask) {
+    int rc = sphb_upload_aos(e, particles, n, stride);
+    if (rc) return rc;
+    if ((rc = sphb_step(e, nsteps))) return rc;
+    return sphb_download_aos(e, particles, n, stride, field_mask); // synchronises
+}
+
+int sphb_synchronize(sphb_engine* e) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    int rc = use_device(e);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    return SPHB_OK;
+}
+
+int sphb_host_register(void* ptr, size_t bytes) {
+    if (!ptr || !bytes) return fail(SPHB_ERR_INVALID, "null range");
+    CK(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return SPHB_OK;
+}
+
+int sphb_host_unregister(void* ptr) {
+    if (!ptr) return fail(SPHB_ERR_INVALID, "null range");
+    CK(cudaHostUnregister(ptr));
+    return SPHB_OK;
+}
+
+int sphb_eval_kernels(sphb_engine* e, const float* xi, const float* xj, size_t count, float* w, float* grad, float* lap) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (count == 0) return SPHB_OK;
+    if (!xi || !xj) return fail(SPHB_ERR_INVALID, "null points");
+    if (count > (1u << 26)) return fail(SPHB_ERR_CAPACITY, "too many pairs");
+    int rc = use_device(e);
+    if (rc) return rc;
+    CK(e->scratch.reserve(count * 11));
+    float* d_xi = e->scratch.p;
+    float* d_xj = d_xi + 3 * count;
+    float* d_w = d_xj + 3 * count;
+    float* d_g = d_w + count;
+    float* d_l = d_g + 3 * count;
+    CK(cudaMemcpyAsync(d_xi, xi, 3 * count * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(d_xj, xj, 3 * count * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    LAUNCH(e, k_eval_kernels, cdiv(count, 256), 256, 0, e->c, d_xi, d_xj, (int)count, d_w, d_g, d_l);
+    CK(cudaGetLastError());
+    if (w) CK(cudaMemcpyAsync(w, d_w, count * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (grad) CK(cudaMemcpyAsync(grad, d_g, 3 * count * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (lap) CK(cudaMemcpyAsync(lap, d_l, count * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return SPHB_OK;
+}
+
+int sphb_get_cells(sphb_engine* e, int32_t* cell_xyz, int32_t* perm, int32_t* dims, float* origin, float* cell) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (!e->grid_valid) return fail(SPHB_ERR_STATE, "no grid: call sphb_update_cells first");
+    const size_t n = e->n;
+    GridDesc g;
+    CK(cudaMemcpyAsync(&g, e->d_grid, sizeof g, cudaMemcpyDeviceToHost, e->stream));
+    if (cell_xyz && n) {
+        CK(e->scratch.reserve(3 * n));
+        LAUNCH(e, k_cells_xyz, cdiv(n, 256), 256, 0, e->d_grid, e->posm[e->cur].p, e->oid[e->cur].p, (int*)e->scratch.p, (int)n);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(cell_xyz, e->scratch.p, 3 * n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    }
+    if (perm && n) CK(cudaMemcpyAsync(perm, e->oid[e->cur].p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    if (dims) { dims[0] = g.dims[0]; dims[1] = g.dims[1]; dims[2] = g.dims[2]; }
+    if (origin) { origin[0] = g.origin[0]; origin[1] = g.origin[1]; origin[2] = g.origin[2]; }
+    if (cell) *cell = g.cell[0];
+    return SPHB_OK;
+}
+
+int sphb_get_bbox(sphb_engine* e, float bbox[6]) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (!bbox) return fail(SPHB_ERR_INVALID, "null bbox");
+    if (e->n == 0) return fail(SPHB_ERR_STATE, "no particles");
+    if (!e->bbox_valid && (rc = run_bbox(e))) return rc;
+    BBoxAcc acc;
+    CK(cudaMemcpyAsync(&acc, e->d_bbox, sizeof acc, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    for (int a = 0; a < 3; a++) {
+        unsigned int lo = acc.lo[a], hi = acc.hi[a];
+        unsigned int bl = (lo & 0x80000000u) ? (lo & 0x7fffffffu) : ~lo;
+        unsigned int bh = (hi & 0x80000000u) ? (hi & 0x7fffffffu) : ~hi;
+        memcpy(&bbox[a], &bl, 4);
+        memcpy(&bbox[3 + a], &bh, 4);
+    }
+    return SPHB_OK;
+}
+
+size_t sphb_count(const sphb_engine* e) { return e ? e->n : 0; }
+
+int sphb_enable_timing(sphb_engine* e, int on) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    int rc = use_device(e);
+    if (rc) return rc;
+    if (on && !e->ev) {
+        e->ev = new (std::nothrow) cudaEvent_t[4 * sphb_engine::kMaxTimed]();
+        if (!e->ev) return fail(SPHB_ERR_INVALID, "out of host memory");
+        for (int i = 0; i < 4 * sphb_engine::kMaxTimed; i++) CK(cudaEventCreate(&e->ev[i]));
+    }
+    e->timing = on != 0;
+    e->timed_steps = 0;
+    return SPHB_OK;
+}
+
+int sphb_get_timing(sphb_engine* e, float ms[4], int* steps) {
+    if (!e || !ms) return fail(SPHB_ERR_INVALID, "null argument");
+    int rc = use_device(e);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    double acc[4] = {0, 0, 0, 0};
+    for (int s = 0; s < e->timed_steps; s++) {
+        cudaEvent_t* ev = e->ev + 4 * s;
+        float t;
+        CK(cudaEventElapsedTime(&t, ev[0], ev[1])); acc[0] += t;
+        CK(cudaEventElapsedTime(&t, ev[1], ev[2])); acc[1] += t;
+        CK(cudaEventElapsedTime(&t, ev[2], ev[3])); acc[2] += t;
+        CK(cudaEventElapsedTime(&t, ev[0], ev[3])); acc[3] += t;
+    }
+    for (int k = 0; k < 4; k++) ms[k] = e->timed_steps ? (float)(acc[k] / e->timed_steps) : 0.0f;
+    if (steps) *steps = e->timed_steps;
+    return SPHB_OK;
+}
+
+uint64_t sphb_launch_count(const sphb_engine* e) { return e ? e->launches : 0; }
+
+int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, void** accel, int32_t** ids) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    const int cur = e->cur;
+    if (posm) *posm = e->posm[cur].p;
+    if (vel) *vel = e->vel[cur].p;
+    if (aux) *aux = e->aux[cur].p;
+    if (accel) *accel = e->accel[cur].p;
+    if (ids) *ids = e->oid[cur].p;
+    return SPHB_OK;
+}
+
+void* sphb_stream(sphb_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+} // extern "C"
