@@ -180,7 +180,7 @@ def run_reference_arm(args):
             "data": "synthetic", "config": {"workload": WORKLOADS[args.workload], "sample_particles": len(ps)},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line, default=float), flush=True)
 
 
 def main():
@@ -299,7 +299,7 @@ def main():
         "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "step": float(phase[3])},
         "cpu_baseline": cpu,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line, default=float), flush=True)
     eng.close()
 
 

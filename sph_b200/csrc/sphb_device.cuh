@@ -344,27 +344,32 @@ __device__ __forceinline__ float w_shape(const Consts& c, float d2) {
     return t * t * t;
 }
 
-// Visits every candidate run [jb, je) of sorted slots in the (2S+1)^2 rows around cell (cx,cy,cz).
-// Along x the 2S+1 cells of a row are contiguous in the sorted arrays, so a row is one run.
-template <class F>
-__device__ __forceinline__ void for_each_run(const GridDesc& g, const int* __restrict__ cell_start, int cx, int cy, int cz, F&& f) {
-    const int S = g.stencil;
+// Candidate runs.  Around cell (cx,cy,cz) there are (2S+1)^2 rows (dz, dy); along x the 2S+1 cells of a
+// row are contiguous in the sorted arrays, so each row is ONE run [jb, je) of sorted slots.  Rows are
+// numbered canonically r = (dz+S)*(2S+1) + (dy+S) so that the density and force kernels agree on them;
+// a row outside the grid is the empty run.
+__device__ __forceinline__ void row_run(const GridDesc& g, const int* __restrict__ cell_start, int cx, int cy, int cz, int r,
+                                        int& jb, int& je) {
+    const int S = g.stencil, W = 2 * S + 1;
+    const int z = cz + r / W - S, y = cy + r % W - S;
+    jb = je = 0;
+    if (z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]) return;
     const int x0 = max(cx - S, 0), x1 = min(cx + S, g.dims[0] - 1);
-    const int z0 = max(cz - S, 0), z1 = min(cz + S, g.dims[2] - 1);
-    const int y0 = max(cy - S, 0), y1 = min(cy + S, g.dims[1] - 1);
-    for (int z = z0; z <= z1; z++) {
-        for (int y = y0; y <= y1; y++) {
-            const int row = g.dims[0] * (y + g.dims[1] * z);
-            const int jb = __ldg(cell_start + row + x0);
-            const int je = __ldg(cell_start + row + x1 + 1);
-            f(jb, je);
-        }
-    }
+    const int row = g.dims[0] * (y + g.dims[1] * z);
+    jb = __ldg(cell_start + row + x0);
+    je = __ldg(cell_start + row + x1 + 1);
 }
 
+// Neighbour masks.  While the density kernel tests every candidate of a run against the support radius
+// anyway, it records the outcome as one bit per candidate: mask[r*n + i] bit k  <=>  sorted slot jb_r + k
+// is a neighbour of i (d2 < R^2, k < 64, self excluded).  The force kernel then visits neighbours only --
+// no distance test on the ~85 % of candidates that fail it -- and its lanes stay converged on the heavy
+// pair body.  Candidates beyond the 64th of a run (crowded cells) are re-tested by the force kernel.
+constexpr int kMaskBits = 64;
+
 // ---------------------------------------------------------------------------------------------------
-// K4: density + equation of state (SphUtils.cpp:100-149).  One thread per sorted particle.
-// aux = (rho, P, sqrt|P/rho|, 1/rho): the last two are precomputed for the force kernel
+// K4: density + equation of state (SphUtils.cpp:100-149) + neighbour masks.  One thread per sorted
+// particle.  aux = (rho, P, sqrt|P/rho|, 1/rho): the last two are precomputed for the force kernel
 // (SphUtils.cpp:223 evaluates sqrt|P/rho| per pair).
 
 __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
@@ -375,27 +380,62 @@ __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
     return make_float4(rho, P, sqrtf(fabsf(__fdiv_rn(P, rho))), inv);
 }
 
+// kAux: compute and store density/pressure.  kMask: store the neighbour masks.
+template <bool kAux, bool kMask>
 __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
-                                                 const float4* __restrict__ posm, float4* __restrict__ aux, int n) {
+                                                 const float4* __restrict__ posm, float4* __restrict__ aux,
+                                                 unsigned long long* __restrict__ mask, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const GridDesc g = *gd;
     const float4 pi = ldg4(posm + i);
     int cx, cy, cz;
     cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
+    const int nrows = (2 * g.stencil + 1) * (2 * g.stencil + 1);
     float sum = 0.0f;
-    for_each_run(g, cell_start, cx, cy, cz, [&](int jb, int je) {
+    for (int r = 0; r < nrows; r++) {
+        int jb, je;
+        row_run(g, cell_start, cx, cy, cz, r, jb, je);
+        const int jm = min(je, jb + kMaskBits);
+        unsigned int m0 = 0, m1 = 0; // bits enter at the top and slide down: after len steps bit k = candidate k
+        int j = jb;
+        const int jh = min(jm, jb + 32);
 #pragma unroll 4
-        for (int j = jb; j < je; j++) {
+        for (; j < jh; j++) {
             const float4 pj = ldg4(posm + j);
             const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
             const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-            float w = w_shape(c, d2);
-            w = (j == i) ? 0.0f : w; // the self term is excluded by index (SphUtils.cpp:132)
-            sum = fmaf(pj.w, w, sum);
+            if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
+            if (kMask) m0 = (m0 >> 1) | (!(d2 >= c.R2) ? 0x80000000u : 0u);
         }
-    });
-    aux[i] = finish_density(c, sum);
+        if (kMask) m0 = (jh - jb) ? (m0 >> (32 - (jh - jb))) : 0u;
+#pragma unroll 4
+        for (; j < jm; j++) {
+            const float4 pj = ldg4(posm + j);
+            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+            if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
+            if (kMask) m1 = (m1 >> 1) | (!(d2 >= c.R2) ? 0x80000000u : 0u);
+        }
+        if (kMask) m1 = (jm - jh) > 0 ? (m1 >> (32 - (jm - jh))) : 0u;
+        if (kAux)
+            for (; j < je; j++) { // beyond the mask: crowded run
+                const float4 pj = ldg4(posm + j);
+                const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                sum = fmaf(pj.w, w_shape(c, fmaf(dx, dx, fmaf(dy, dy, dz * dz))), sum);
+            }
+        if (kMask) {
+            unsigned long long m = ((unsigned long long)m1 << 32) | m0;
+            const int self = i - jb; // the self term is excluded by index (SphUtils.cpp:132,216)
+            if (self >= 0 && self < kMaskBits && i < je) m &= ~(1ull << self);
+            mask[(size_t)r * n + i] = m;
+        }
+    }
+    if (kAux) {
+        // self term: every run above included j == i exactly once (its own cell's row); take it out again
+        sum -= pi.w * (c.h2 * c.h2 * c.h2);
+        aux[i] = finish_density(c, sum);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -459,12 +499,21 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
 //         thread reads only old buffers, so the fusion is race-free).
 // kBBox:  also fold the new positions into the bounding box for the next step's grid.
 // kAccel: store the acceleration (parity, viewers).
-template <bool kFused, bool kBBox, bool kAccel>
+// kRows:  (2S+1)^2, 9 for cell >= R, 25 for cell >= R/2.
+// Each thread walks the set bits of its particle's neighbour masks (written by k_density) as ONE stream
+// across the rows, so the lanes of a warp stay together on the pair body however the neighbours are
+// spread over the rows.  Masks and run starts are staged per thread in shared memory (column tid: no
+// conflicts, no barrier needed).
+template <bool kFused, bool kBBox, bool kAccel, int kRows>
 __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
+                                               const unsigned long long* __restrict__ mask,
                                                float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                BBoxAcc* bbox, int n) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ unsigned long long s_mask[kRows][128];
+    __shared__ int s_jb[kRows][128];
+    const int tid = threadIdx.x;
+    const int i = blockIdx.x * blockDim.x + tid;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     if (i < n) {
         const GridDesc g = *gd;
@@ -473,20 +522,47 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         const float4 ai = ldg4(aux + i);
         int cx, cy, cz;
         cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
+        bool crowded = false;
+#pragma unroll
+        for (int r = 0; r < kRows; r++) {
+            int jb, je;
+            row_run(g, cell_start, cx, cy, cz, r, jb, je);
+            s_jb[r][tid] = jb;
+            s_mask[r][tid] = mask[(size_t)r * n + i];
+            crowded |= (je - jb) > kMaskBits;
+        }
         float ax = 0.0f, ay = 0.0f, az = 0.0f;
-        for_each_run(g, cell_start, cx, cy, cz, [&](int jb, int je) {
-            for (int j = jb; j < je; j++) {
-                const float4 pj = ldg4(posm + j);
-                const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-                // q < h  <=>  d2 < h^4; NaN-safe form keeps the reference's NaN for coincident points
-                if (!(d2 >= c.R2) && j != i) {
-                    const float4 vj = ldg4(vel + j);
-                    const float4 aj = ldg4(aux + j);
-                    pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, vj, aj, ax, ay, az);
+        int r = -1, jb = 0;
+        unsigned long long m = 0;
+        for (;;) {
+            while (m == 0 && r < kRows - 1) {
+                ++r;
+                m = s_mask[r][tid];
+                jb = s_jb[r][tid];
+            }
+            if (m == 0) break;
+            const int j = jb + __ffsll((long long)m) - 1;
+            m &= m - 1;
+            const float4 pj = ldg4(posm + j);
+            const float4 vj = ldg4(vel + j);
+            const float4 aj = ldg4(aux + j);
+            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+            pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, vj, aj, ax, ay, az);
+        }
+        if (crowded) { // candidates past the 64th of a run: test them here (rare)
+            for (int rr = 0; rr < kRows; rr++) {
+                int jb2, je2;
+                row_run(g, cell_start, cx, cy, cz, rr, jb2, je2);
+                for (int j = jb2 + kMaskBits; j < je2; j++) {
+                    const float4 pj = ldg4(posm + j);
+                    const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                    const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                    // q < h  <=>  d2 < h^4; NaN-safe form keeps the reference's NaN for coincident points
+                    if (!(d2 >= c.R2) && j != i) pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, ldg4(vel + j), ldg4(aux + j), ax, ay, az);
                 }
             }
-        });
+        }
         ax = fmaf(c.Kg, ax, c.gx);
         ay = fmaf(c.Kg, ay, c.gy);
         az = fmaf(c.Kg, az, c.gz);

@@ -67,6 +67,8 @@ struct sphb_engine {
     DevBuf<int> oid[2];
     DevBuf<int> key, slot, inv;
     DevBuf<int2> pairs;
+    DevBuf<unsigned long long> mask; // neighbour masks, rows x n
+    int rows = 9;                    // (2*stencil+1)^2
     DevBuf<int> cell_start; // max_cells + 1 (+ slack)
     DevBuf<int> block_sums;
     DevBuf<float> aos;      // staging for host AoS records
@@ -78,6 +80,7 @@ struct sphb_engine {
     bool have_state = false;
     bool grid_valid = false; // cell_start / sorted order correspond to the current positions
     bool bbox_valid = false; // d_bbox holds the bbox of the current positions
+    bool mask_valid = false; // neighbour masks correspond to the current sorted positions
     bool aos_valid = false;  // staging holds the bytes of the last AoS upload
     size_t aos_stride_w = 13;
 
@@ -147,6 +150,8 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     CK(e->slot.reserve(want));
     CK(e->inv.reserve(want));
     CK(e->pairs.reserve(want));
+    e->rows = (e->c.cell >= e->c.h2) ? 9 : 25;
+    CK(e->mask.reserve(want * (size_t)e->rows));
     long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)(2 * want + 65536);
     if (mc > (1ll << 30)) mc = 1ll << 30;
     if (mc > e->max_cells) {
@@ -199,15 +204,24 @@ int run_sort(sphb_engine* e, bool carry_all) {
     CK(cudaGetLastError());
     e->cur = nxt;
     e->grid_valid = true;
+    e->mask_valid = false;
     e->bbox_valid = false; // k_key_hist re-armed the accumulator
     return SPHB_OK;
 }
 
-int run_density(sphb_engine* e) {
+// K4.  with_aux = false only rebuilds the neighbour masks (update_forces on an uploaded rho/P).
+int run_density(sphb_engine* e, bool with_aux) {
     const int n = (int)e->n;
-    LAUNCH(e, k_density, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->aux[e->cur].p, n);
+    auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
+    LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->aux[e->cur].p, e->mask.p, n);
     CK(cudaGetLastError());
+    e->mask_valid = true;
     return SPHB_OK;
+}
+
+template <bool kFused, bool kBBox, bool kAccel>
+auto force_kernel(int rows) {
+    return rows == 9 ? k_force<kFused, kBBox, kAccel, 9> : k_force<kFused, kBBox, kAccel, 25>;
 }
 
 int check_ready(sphb_engine* e) {
@@ -284,7 +298,7 @@ void sphb_destroy(sphb_engine* e) {
     for (int b = 0; b < 2; b++) {
         e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
     }
-    e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release();
+    e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release();
     e->cell_start.release(); e->block_sums.release(); e->aos.release(); e->scratch.release();
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
@@ -337,6 +351,7 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
     }
     e->have_state = true;
     e->grid_valid = false;
+    e->mask_valid = false;
     e->bbox_valid = false;
     e->aos_valid = true;
     return SPHB_OK;
@@ -363,6 +378,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
     }
     e->have_state = true;
     e->grid_valid = false;
+    e->mask_valid = false;
     e->bbox_valid = false;
     e->aos_valid = false;
     return SPHB_OK;
@@ -405,7 +421,7 @@ int sphb_update_density(sphb_engine* e) {
     if (rc) return rc;
     if (e->n == 0) return SPHB_OK;
     if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
-    return run_density(e);
+    return run_density(e, true);
 }
 
 int sphb_update_forces(sphb_engine* e) {
@@ -413,10 +429,11 @@ int sphb_update_forces(sphb_engine* e) {
     if (rc) return rc;
     if (e->n == 0) return SPHB_OK;
     if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
+    if (!e->mask_valid && (rc = run_density(e, false))) return rc;
     const int n = (int)e->n, cur = e->cur;
-    auto kfn = k_force<false, false, true>;
+    auto kfn = force_kernel<false, false, true>(e->rows);
     LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p,
-           e->aux[cur].p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
+           e->aux[cur].p, e->mask.p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
     CK(cudaGetLastError());
     return SPHB_OK;
 }
@@ -429,6 +446,7 @@ int sphb_update_posvel(sphb_engine* e) {
     LAUNCH(e, k_posvel, cdiv(n, 256), 256, 0, e->c, e->posm[cur].p, e->vel[cur].p, e->accel[cur].p, n);
     CK(cudaGetLastError());
     e->grid_valid = false;
+    e->mask_valid = false;
     e->bbox_valid = false;
     return SPHB_OK;
 }
@@ -441,6 +459,7 @@ int sphb_collision(sphb_engine* e) {
     LAUNCH(e, k_collision, cdiv(n, 256), 256, 0, e->c, e->posm[cur].p, e->vel[cur].p, n);
     CK(cudaGetLastError());
     e->grid_valid = false;
+    e->mask_valid = false;
     e->bbox_valid = false;
     return SPHB_OK;
 }
@@ -460,13 +479,13 @@ int sphb_step(sphb_engine* e, int nsteps) {
         // Always re-sort: positions moved.  (First step after an upload of an already valid grid is rare.)
         if ((rc = run_sort(e, false))) return rc;
         if (timed) CK(cudaEventRecord(ev[1], e->stream));
-        if ((rc = run_density(e))) return rc;
+        if ((rc = run_density(e, true))) return rc;
         if (timed) CK(cudaEventRecord(ev[2], e->stream));
         const int cur = e->cur, nxt = cur ^ 1;
         const int blocks = cdiv(n, 128);
-#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
-        auto kfn = bbox ? (acc ? k_force<true, true, true> : k_force<true, true, false>)
-                        : (acc ? k_force<true, false, true> : k_force<true, false, false>);
+#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->mask.p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
+        auto kfn = bbox ? (acc ? force_kernel<true, true, true>(e->rows) : force_kernel<true, true, false>(e->rows))
+                        : (acc ? force_kernel<true, false, true>(e->rows) : force_kernel<true, false, false>(e->rows));
         LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS);
 #undef FORCE_ARGS
         CK(cudaGetLastError());
@@ -478,6 +497,7 @@ int sphb_step(sphb_engine* e, int nsteps) {
         }
         e->cur = nxt;
         e->grid_valid = false;
+        e->mask_valid = false;
         e->bbox_valid = bbox;
         if (timed) {
             CK(cudaEventRecord(ev[3], e->stream));
