@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-accel", action="store_true", help="skip the per-particle acceleration output (72 B force kernel)")
     ap.add_argument("--domain", default="fixed", choices=["fixed", "bbox"])
+    ap.add_argument("--cell-frac", type=float, default=1.0, help="grid cell edge as a fraction of the support radius h*h (>= 0.5)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -216,6 +217,9 @@ def main():
     ps, walls, (dlo, dhi) = make_workload(args.workload)
     n = len(ps)
     kw = dict(write_accel=0 if args.no_accel else 1)
+    if args.cell_frac != 1.0:
+        cell = float(np.float32(0.45) * np.float32(0.45)) * args.cell_frac
+        kw.update(cell_size=cell, max_cells=int(np.prod([(h - l) / cell + 2 for l, h in zip(dlo, dhi)])) + 4096)
     if args.domain == "fixed":
         kw.update(domain_mode=sph_b200.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi)
     eng = sph_b200.Engine(device=local, **kw)
@@ -290,7 +294,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload], "particles": n, "domain": args.domain,
+        "config": {"workload": WORKLOADS[args.workload], "particles": n, "domain": args.domain, "cell_frac": args.cell_frac,
                    "l2": "state (>= 32 B/particle x 2 buffers) exceeds the 126 MB L2" if n * 64 > 126e6 else
                          "state fits in L2: no flush between steps (steps are dependent, not repeats)",
                    "accel_output": not args.no_accel},

@@ -68,6 +68,19 @@ __device__ __forceinline__ float ord2f(unsigned int u) {
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
+// MUFU approximations without the denormal fix-up code the C library versions carry (the pair body runs
+// ~40 times per particle per step; magnitudes here are nowhere near 1e-38).  <= 2 ulp each.
+__device__ __forceinline__ float fast_rsqrt(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // Cell coordinate along one axis.  Same expression as SphUtils.cpp:38-40, floor((p - min) / cell), in
 // IEEE float (no FMA, true division), then clamped to the grid so that strays stay adjacent to their
 // neighbours.  Bit-exact against the CPU grid build the tests use.
@@ -361,8 +374,8 @@ __device__ __forceinline__ void row_run(const GridDesc& g, const int* __restrict
 }
 
 // Neighbour masks.  While the density kernel tests every candidate of a run against the support radius
-// anyway, it records the outcome as one bit per candidate: mask[r*n + i] bit k  <=>  sorted slot jb_r + k
-// is a neighbour of i (d2 < R^2, k < 64, self excluded).  The force kernel then visits neighbours only --
+// anyway, it records the outcome as one bit per candidate, two 32-bit words per row:
+// mask[(2r+w)*n + i] bit k  <=>  sorted slot jb_r + 32w + k is a neighbour of i (d2 < R^2, self excluded).  The force kernel then visits neighbours only --
 // no distance test on the ~85 % of candidates that fail it -- and its lanes stay converged on the heavy
 // pair body.  Candidates beyond the 64th of a run (crowded cells) are re-tested by the force kernel.
 constexpr int kMaskBits = 64;
@@ -384,7 +397,7 @@ __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
 template <bool kAux, bool kMask>
 __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                  const float4* __restrict__ posm, float4* __restrict__ aux,
-                                                 unsigned long long* __restrict__ mask, int n) {
+                                                 unsigned int* __restrict__ mask, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const GridDesc g = *gd;
@@ -425,10 +438,13 @@ __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __res
                 sum = fmaf(pj.w, w_shape(c, fmaf(dx, dx, fmaf(dy, dy, dz * dz))), sum);
             }
         if (kMask) {
-            unsigned long long m = ((unsigned long long)m1 << 32) | m0;
             const int self = i - jb; // the self term is excluded by index (SphUtils.cpp:132,216)
-            if (self >= 0 && self < kMaskBits && i < je) m &= ~(1ull << self);
-            mask[(size_t)r * n + i] = m;
+            if (self >= 0 && i < je) {
+                if (self < 32) m0 &= ~(1u << self);
+                else if (self < kMaskBits) m1 &= ~(1u << (self - 32));
+            }
+            mask[(size_t)(2 * r) * n + i] = m0;      // word w of row r covers candidates jb + 32*w ...
+            mask[(size_t)(2 * r + 1) * n + i] = m1;
         }
     }
     if (kAux) {
@@ -447,14 +463,14 @@ __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __res
 __device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, float dz, float d2, const float4& vi, const float4& ai,
                                            float mj, const float4& vj, const float4& aj, float& ax, float& ay, float& az) {
     const float vdotr = fmaf(vi.x - vj.x, dx, fmaf(vi.y - vj.y, dy, (vi.z - vj.z) * dz)); // :220
-    const float rinv = rsqrtf(d2);
+    const float rinv = fast_rsqrt(d2);
     const float r = d2 * rinv;
     const float s = fmaf(-r, c.inv_h, c.h); // h - q, q = r/h              (:70-74)
     float visc = 0.0f;
     if (vdotr < 0.0f) {                                                                  // :222-227
         const float cbar = 0.5f * (ai.z + aj.z);
-        const float mu = __fdividef(c.h * vdotr, d2 + c.eta_h2);
-        visc = __fdividef(2.0f * mu * fmaf(c.beta, mu, -c.alpha * cbar), ai.x + aj.x);
+        const float mu = c.h * vdotr * fast_rcp(d2 + c.eta_h2);
+        visc = 2.0f * mu * fmaf(c.beta, mu, -c.alpha * cbar) * fast_rcp(ai.x + aj.x);
     }
     // :228  -(m_j) * (pi + (P_i + P_j) / (2 rho_j rho_i)); ai.w, aj.w = 1/rho
     const float t = -mj * fmaf(0.5f * (ai.y + aj.y), ai.w * aj.w, visc);
@@ -507,10 +523,10 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
 template <bool kFused, bool kBBox, bool kAccel, int kRows>
 __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
-                                               const unsigned long long* __restrict__ mask,
+                                               const unsigned int* __restrict__ mask,
                                                float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                BBoxAcc* bbox, int n) {
-    __shared__ unsigned long long s_mask[kRows][128];
+    __shared__ unsigned int s_mask[2 * kRows][128];
     __shared__ int s_jb[kRows][128];
     const int tid = threadIdx.x;
     const int i = blockIdx.x * blockDim.x + tid;
@@ -528,20 +544,21 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             int jb, je;
             row_run(g, cell_start, cx, cy, cz, r, jb, je);
             s_jb[r][tid] = jb;
-            s_mask[r][tid] = mask[(size_t)r * n + i];
+            s_mask[2 * r][tid] = mask[(size_t)(2 * r) * n + i];
+            s_mask[2 * r + 1][tid] = mask[(size_t)(2 * r + 1) * n + i];
             crowded |= (je - jb) > kMaskBits;
         }
         float ax = 0.0f, ay = 0.0f, az = 0.0f;
-        int r = -1, jb = 0;
-        unsigned long long m = 0;
+        int w = -1, jb = 0; // w: current mask word (row w/2, half w&1)
+        unsigned int m = 0;
         for (;;) {
-            while (m == 0 && r < kRows - 1) {
-                ++r;
-                m = s_mask[r][tid];
-                jb = s_jb[r][tid];
+            while (m == 0 && w < 2 * kRows - 1) {
+                ++w;
+                m = s_mask[w][tid];
+                jb = s_jb[w >> 1][tid] + ((w & 1) << 5);
             }
             if (m == 0) break;
-            const int j = jb + __ffsll((long long)m) - 1;
+            const int j = jb + __ffs((int)m) - 1;
             m &= m - 1;
             const float4 pj = ldg4(posm + j);
             const float4 vj = ldg4(vel + j);

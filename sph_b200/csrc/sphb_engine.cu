@@ -67,7 +67,7 @@ struct sphb_engine {
     DevBuf<int> oid[2];
     DevBuf<int> key, slot, inv;
     DevBuf<int2> pairs;
-    DevBuf<unsigned long long> mask; // neighbour masks, rows x n
+    DevBuf<unsigned int> mask;       // neighbour masks, 2 words x rows x n
     int rows = 9;                    // (2*stencil+1)^2
     DevBuf<int> cell_start; // max_cells + 1 (+ slack)
     DevBuf<int> block_sums;
@@ -151,7 +151,7 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     CK(e->inv.reserve(want));
     CK(e->pairs.reserve(want));
     e->rows = (e->c.cell >= e->c.h2) ? 9 : 25;
-    CK(e->mask.reserve(want * (size_t)e->rows));
+    CK(e->mask.reserve(want * (size_t)e->rows * 2));
     long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)(2 * want + 65536);
     if (mc > (1ll << 30)) mc = 1ll << 30;
     if (mc > e->max_cells) {

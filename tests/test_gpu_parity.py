@@ -244,6 +244,46 @@ def test_pair_force_antisymmetry(eng):
     assert np.all(np.abs(tot) <= 1e-5 * scale)
 
 
+@pytest.mark.parametrize("frac", [0.5, 0.75, 1.3])
+def test_other_cell_sizes(oracle, golden, frac):
+    """cell = frac * R: a 5x5x5 stencil below 1 (25 runs per particle), fewer, fatter cells above."""
+    g = golden("block4096.npz")
+    R = float(np.float32(0.45) * np.float32(0.45))
+    with sph_b200.Engine(cell_size=R * frac) as e:
+        ps = g["initial"].copy()
+        e.upload(ps)
+        e.update_density()
+        e.update_forces()
+        e.download(ps, F_ALL)
+        want = g["forces"]
+        assert rel_rho(ps["density"], want["density"]) <= RHO_TOL
+        _, normd = accel_errors(ps["accel"], want["accel"], sum_abs_terms(oracle, want))
+        assert normd <= 2e-3
+        # force kernel alone, fed the reference's density
+        ps = g["density"].copy()
+        e.upload(ps)
+        e.update_forces()
+        e.download(ps, sph_b200.F_ACCEL)
+        _, normd = accel_errors(ps["accel"], want["accel"], sum_abs_terms(oracle, want))
+        assert normd <= ACC_TOL
+        xyz, perm, dims, origin, cell = e.get_cells()
+        xyz_o, _, perm_o, _ = oracle.grid_build(oracle.make_grid(origin, cell, dims), g["density"])
+        assert np.array_equal(xyz, xyz_o) and np.array_equal(perm, perm_o)
+
+
+def test_crowded_runs_beyond_the_mask(eng, oracle):
+    """More than 64 candidates in one run: the force kernel re-tests the overflow (kMaskBits)."""
+    rng = np.random.default_rng(11)
+    pos = (np.float32(0.5) + rng.uniform(0, 0.25, (600, 3))).astype(np.float32)      # ~600 particles in ~2 cells
+    ps = scenes.make_particles(pos, rng.normal(scale=0.1, size=(600, 3)).astype(np.float32))
+    want = ps.copy()
+    oracle.update_density(want); oracle.update_forces(want)
+    eng.upload(ps); eng.update_density(); eng.update_forces(); eng.download(ps, F_ALL)
+    assert rel_rho(ps["density"], want["density"]) <= RHO_TOL
+    _, normd = accel_errors(ps["accel"], want["accel"], sum_abs_terms(oracle, want))
+    assert normd <= 2e-3
+
+
 # --------------------------------------------------------------------------------------------------
 # integration and walls: bit-exact given the same inputs
 
