@@ -1,0 +1,93 @@
+// Headless driver: the reference's scene set-up and step loop (SPH/main.cpp initScene :555-559,
+// initParticles :490-505, addParticle :424-442, initWalls :508-540, step_scene :280-303) with every GL /
+// GLUT call left out, driving the engine through the drop-in SphUtils class exactly as main.cpp does.
+//   sph_headless [steps=20] [fused]
+// "fused" uses SphUtils::step_scene (one sphb_step_aos call per step) instead of the four methods.
+// Prints particle count and, per reported step, mean density, kinetic energy and the FNV-1a-64 hash of the
+// position bits (the same hash tests/golden/default_scene.npz holds for the compiled reference).
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "SphUtils.hpp"
+
+#define MAX_PARTICLES 1300
+
+const float dt = 0.033f;
+const float smooth_length = 0.45;
+const float rho0 = 10.0f;
+const float c = 100.0f;
+const float epsilon = 0.01f;
+
+SphUtils sph(smooth_length, rho0, c, dt, epsilon);   // a global, as at main.cpp:62
+std::vector<Particle> particles;
+std::vector<Wall> walls;
+std::vector<Sphere> spheres;
+
+static void addParticle(glm::vec3 x, glm::vec3 v) {
+    float density = rho0 + epsilon;
+    float mass = .1f * smooth_length * smooth_length * smooth_length * rho0;
+    Particle part(x, v, glm::vec3(0.0f, 0.0f, 0.0f), mass, density, 1.0f, 1.0f);
+    if (particles.size() < MAX_PARTICLES) particles.push_back(part);
+}
+
+static void initScene() {
+    float max = 0.9;
+    float min = -0.9;
+    for (float i = min; i <= max; i += 0.1)
+        for (float j = -0.9; j <= -0.6; j += 0.1)
+            for (float k = min; k <= max; k += 0.1) addParticle(glm::vec3(i, j, k), glm::vec3(0, 0, 0));
+    // centre, normal; pushed as w1, w2, w4, w5, w3
+    walls.push_back(Wall(glm::vec3(-1.0f, 0.0f, 0.0f), glm::vec3(1.0f, 0.0f, 0.0f), 1.0f, 1.0f));
+    walls.push_back(Wall(glm::vec3(1.0f, 0.0f, 0.0f), glm::vec3(-1.0f, 0.0f, 0.0f), 1.0f, 1.0f));
+    walls.push_back(Wall(glm::vec3(0.0f, 0.0f, 1.0f), glm::vec3(0.0f, 0.0f, -1.0f), 1.0f, 1.0f));
+    walls.push_back(Wall(glm::vec3(0.0f, 0.0f, -1.0f), glm::vec3(0.0f, 0.0f, 1.0f), 1.0f, 1.0f));
+    walls.push_back(Wall(glm::vec3(0.0f, -1.0f, 0.0f), glm::vec3(0.0f, 1.0f, 0.0f), 1.0f, 1.0f));
+}
+
+static void step_scene(bool fused) {
+    if (fused) {
+        sph.step_scene(particles, walls, 1);
+        return;
+    }
+    sph.update_density(particles);
+    sph.update_forces(particles, spheres);
+    sph.update_posvel(particles, spheres);
+    sph.collision(particles, walls, spheres);
+}
+
+static uint64_t fnv_pos() {
+    uint64_t h = 0xcbf29ce484222325ULL;
+    for (size_t i = 0; i < particles.size(); i++) {
+        float p[3] = {particles[i].pos.x, particles[i].pos.y, particles[i].pos.z};
+        for (int a = 0; a < 3; a++) {
+            uint32_t w;
+            memcpy(&w, &p[a], 4);
+            h ^= w;
+            h *= 0x100000001b3ULL;
+        }
+    }
+    return h;
+}
+
+int main(int argc, char** argv) {
+    int steps = argc > 1 ? atoi(argv[1]) : 20;
+    bool fused = argc > 2 && strcmp(argv[2], "fused") == 0;
+    initScene();
+    printf("particles %zu walls %zu\n", particles.size(), walls.size());
+    if (!sph.engine()) return 2;
+    for (int s = 1; s <= steps; s++) {
+        step_scene(fused);
+        if (s == 1 || s == 2 || s == 10 || s == 20 || s == 100 || s == steps) {
+            double rho = 0.0, ke = 0.0;
+            for (size_t i = 0; i < particles.size(); i++) {
+                const Particle& q = particles[i];
+                rho += q.density;
+                ke += 0.5 * q.mass * ((double)q.vel.x * q.vel.x + (double)q.vel.y * q.vel.y + (double)q.vel.z * q.vel.z);
+            }
+            printf("step %d mean_rho %.6f ke %.6f fnv %016llx\n", s, rho / particles.size(), ke, (unsigned long long)fnv_pos());
+        }
+    }
+    return 0;
+}

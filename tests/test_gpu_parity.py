@@ -437,3 +437,26 @@ def test_determinism(golden):
             e.step_aos(ps, 5)
         outs.append(ps.tobytes())
     assert outs[0] == outs[1]
+
+
+# --------------------------------------------------------------------------------------------------
+# the C++ drop-in (sph_b200/host/SphUtils.hpp) driven like main.cpp drives the reference
+
+@pytest.mark.parametrize("mode", ["methods", "fused"])
+def test_headless_cpp_driver(golden, mode):
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "sph_b200", "host", "sph_headless")
+    if not os.path.exists(exe):
+        pytest.fail("sph_b200/host/sph_headless not built: run __graft_entry__.build()")
+    out = subprocess.run([exe, "20"] + (["fused"] if mode == "fused" else []), capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    lines = out.stdout.strip().splitlines()
+    assert lines[0].split() == ["particles", "972", "walls", "5"]
+    rows = {int(l.split()[1]): l.split() for l in lines[1:]}
+    g = golden("default_scene.npz")
+    assert int(rows[1][7], 16) == int(g["fnv"][0])                           # free fall: the reference's exact floats
+    assert int(rows[2][7], 16) == int(g["fnv"][1])
+    assert int(rows[10][7], 16) == int(g["fnv"][2])
+    assert float(rows[20][3]) == pytest.approx(float(g["stats"][3][0]), abs=1e-3)    # mean rho after 20 steps
+    assert float(rows[20][5]) == pytest.approx(float(g["stats"][3][2]), rel=1e-2)    # kinetic energy
