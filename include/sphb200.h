@@ -172,6 +172,39 @@ int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, v
 /* The CUDA stream (cudaStream_t) all of this engine's work is enqueued on. */
 void* sphb_stream(sphb_engine* e);
 
+/* --- allocation-free bounding box ------------------------------------------------------------------ */
+
+/* Largest point count sphb_bbox_noalloc accepts (its scratch is a fixed array inside the library). */
+#define SPHB_NOALLOC_MAX_POINTS 4194304
+
+/*
+ * Bounding box of `n` device-resident points without allocating anything.  (No counterpart in the
+ * reference: it exists for callers that are not allowed to allocate GPU memory at the moment they need the
+ * box -- a render or real-time thread that must not hit the device-wide synchronisation cudaMalloc/cudaFree
+ * imply, a plug-in running under a host application's fixed memory budget, code running after the
+ * application has handed all remaining memory to another library.  Every other entry point of this library
+ * works on an engine, and engines own buffers that they create and grow with cudaMalloc.)
+ *
+ *   posm_device  n float4 records (x, y, z, anything) in device memory of the CURRENT device, e.g. the
+ *                `posm` pointer of sphb_get_device_state, or a mapped vertex buffer
+ *   bbox_device  6 floats in device memory, written as {minx, miny, minz, maxx, maxy, maxz}; NaN
+ *                coordinates are skipped like sphb_get_bbox does; with no finite point the result is
+ *                {+inf x3, -inf x3}
+ *   stream       cudaStream_t to enqueue on (NULL = the default stream).  The call returns after
+ *                enqueueing; the result is ready when the stream reaches that point.
+ *
+ * The per-block partial results live in one file-scope __device__ array of the library
+ * (SPHB_NOALLOC_MAX_POINTS / 1024 blocks x 32 B = 128 KB, plus a 256-byte control block), which every GPU
+ * that loads the library holds until the process exits.  Consequences the caller must respect:
+ *   - n > SPHB_NOALLOC_MAX_POINTS (or n == 0) is refused with SPHB_ERR_CAPACITY / SPHB_ERR_INVALID;
+ *   - all calls on one GPU share that array: two calls whose kernels may run at the same time (different
+ *     streams, different host threads) race and can return wrong boxes -- serialise them;
+ *   - the FIRST call on each device looks the array's device address up (cudaGetSymbolAddress, with that
+ *     device current) and caches it; make that first call before starting any stream capture.
+ * Calls no cudaMalloc / cudaFree / library allocator, creates no stream or event.
+ */
+int sphb_bbox_noalloc(const void* posm_device, size_t n, void* stream, float* bbox_device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,6 +25,7 @@ SPHERE = np.dtype([("pos", "<f4", 3), ("vel", "<f4", 3), ("accel", "<f4", 3), ("
 
 F_POS, F_VEL, F_ACCEL, F_DENSITY, F_ALL = 1, 2, 4, 8, 15
 DOMAIN_BBOX, DOMAIN_FIXED = 0, 1
+NOALLOC_MAX_POINTS = 4194304   # SPHB_NOALLOC_MAX_POINTS
 
 
 class SphbError(RuntimeError):
@@ -52,7 +53,7 @@ EXPORTS = [
     "sphb_update_posvel", "sphb_collision", "sphb_step", "sphb_step_aos", "sphb_synchronize",
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
-    "sphb_get_device_state", "sphb_stream",
+    "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc",
 ]
 
 _lib = None
@@ -103,6 +104,7 @@ def load_library() -> C.CDLL:
     L.sphb_get_device_state.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     L.sphb_stream.argtypes = [vp]
     L.sphb_stream.restype = vp
+    L.sphb_bbox_noalloc.argtypes = [vp, sz, vp, vp]
     _lib = L
     return L
 

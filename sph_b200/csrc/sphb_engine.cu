@@ -650,3 +650,124 @@ int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, v
 void* sphb_stream(sphb_engine* e) { return e ? (void*)e->stream : nullptr; }
 
 } // extern "C"
+
+// =====================================================================================================
+// Allocation-free bounding box (include/sphb200.h: sphb_bbox_noalloc).  Self-contained: it shares no
+// code path with the engine above.
+//
+// Scratch = one file-scope __device__ array.  In HOST code the name `g_noalloc_scratch` is only a
+// stand-in for the symbol, not a device address: the address each device gave the array is fetched once
+// per device with cudaGetSymbolAddress (that device current) and passed to the kernel as a plain pointer.
+
+namespace {
+
+constexpr int kNaThreads = 256;
+constexpr int kNaPerBlock = 1024;                                   // points per block (4 per thread)
+constexpr int kNaMaxBlocks = SPHB_NOALLOC_MAX_POINTS / kNaPerBlock; // 4096
+constexpr int kNaPartialFloats = 8;                                 // 6 used, padded to 32 B
+constexpr int kNaCtrlFloats = 64;                                   // 256-byte control block: word 0 = arrival counter
+constexpr int kNaMaxDevices = 64;
+
+static __device__ __align__(256) float g_noalloc_scratch[kNaCtrlFloats + kNaMaxBlocks * kNaPartialFloats];
+
+float* g_noalloc_ptr[kNaMaxDevices]; // per-device address of the array above, 0 until looked up
+
+// One block folds 1024 points into 6 numbers and parks them in the scratch; the block that arrives last
+// folds all the parked partials into the caller's output.  `ctrl[0]` (arrival counter) must be zero when
+// the kernel starts: the entry point clears it on the same stream before every launch.
+__global__ void __launch_bounds__(kNaThreads) k_bbox_noalloc(const float4* __restrict__ posm, int n, float* scratch, float* __restrict__ out) {
+    __shared__ float s_lo[3][kNaThreads / 32], s_hi[3][kNaThreads / 32];
+    __shared__ bool s_last;
+    unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
+    float* partial = scratch + kNaCtrlFloats;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    const int base = blockIdx.x * kNaPerBlock;
+#pragma unroll
+    for (int k = 0; k < kNaPerBlock / kNaThreads; k++) {
+        const int i = base + k * kNaThreads + threadIdx.x;
+        if (i < n) {
+            const float4 p = __ldg(posm + i);
+            lo[0] = fminf(lo[0], p.x); hi[0] = fmaxf(hi[0], p.x); // fminf/fmaxf ignore NaN operands
+            lo[1] = fminf(lo[1], p.y); hi[1] = fmaxf(hi[1], p.y);
+            lo[2] = fminf(lo[2], p.z); hi[2] = fmaxf(hi[2], p.z);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+        if (lane == 0) { s_lo[a][warp] = lo[a]; s_hi[a][warp] = hi[a]; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float* mine = partial + (size_t)blockIdx.x * kNaPartialFloats;
+        for (int a = 0; a < 3; a++) {
+            float l = INFINITY, h = -INFINITY;
+            for (int w = 0; w < kNaThreads / 32; w++) { l = fminf(l, s_lo[a][w]); h = fmaxf(h, s_hi[a][w]); }
+            mine[a] = l;
+            mine[3 + a] = h;
+        }
+        __threadfence();                                       // partials visible before the ticket is taken
+        s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    float l[3] = {INFINITY, INFINITY, INFINITY}, h[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += kNaThreads) {
+        const volatile float* q = partial + (size_t)b * kNaPartialFloats;
+#pragma unroll
+        for (int a = 0; a < 3; a++) { l[a] = fminf(l[a], q[a]); h[a] = fmaxf(h[a], q[3 + a]); }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            l[a] = fminf(l[a], __shfl_xor_sync(0xffffffffu, l[a], o));
+            h[a] = fmaxf(h[a], __shfl_xor_sync(0xffffffffu, h[a], o));
+        }
+        if (lane == 0) { s_lo[a][warp] = l[a]; s_hi[a][warp] = h[a]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const int a = threadIdx.x;
+        float ll = INFINITY, hh = -INFINITY;
+        for (int w = 0; w < kNaThreads / 32; w++) { ll = fminf(ll, s_lo[a][w]); hh = fmaxf(hh, s_hi[a][w]); }
+        out[a] = ll;
+        out[3 + a] = hh;
+    }
+    if (threadIdx.x == 0) *counter = 0u; // leave the counter clean for the next call as well
+}
+
+} // namespace
+
+extern "C" int sphb_bbox_noalloc(const void* posm_device, size_t n, void* stream, float* bbox_device) {
+    if (!posm_device || !bbox_device) return fail(SPHB_ERR_INVALID, "sphb_bbox_noalloc: null pointer");
+    if (n == 0) return fail(SPHB_ERR_INVALID, "sphb_bbox_noalloc: no points");
+    if (n > (size_t)SPHB_NOALLOC_MAX_POINTS)
+        return fail(SPHB_ERR_CAPACITY, "sphb_bbox_noalloc: %zu points exceed the fixed scratch (at most %d); use an engine and sphb_get_bbox",
+                    n, SPHB_NOALLOC_MAX_POINTS);
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNaMaxDevices) return fail(SPHB_ERR_INVALID, "sphb_bbox_noalloc: device ordinal %d unsupported", dev);
+    if (!g_noalloc_ptr[dev]) {
+        // set-up, once per device, with that device current: ask the runtime where this device keeps the array
+        float* ptr = nullptr;
+        CK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        if (!ptr) return fail(SPHB_ERR_CUDA, "sphb_bbox_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[dev] = ptr;
+    }
+    float* scratch = g_noalloc_ptr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps whatever the previous call left: the arrival counter is the one word that must be zero
+    CK(cudaMemsetAsync(scratch, 0, sizeof(unsigned int), st));
+    const int blocks = (int)((n + kNaPerBlock - 1) / kNaPerBlock);
+    k_bbox_noalloc<<<blocks, kNaThreads, 0, st>>>((const float4*)posm_device, (int)n, scratch, bbox_device);
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
