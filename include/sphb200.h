@@ -105,7 +105,8 @@ int sphb_set_walls(sphb_engine* e, const void* walls, size_t count, size_t strid
  * (main.cpp:441 grows the vector).  Particle order is remembered: downloads return it. */
 int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stride);
 
-/* Device SoA -> host AoS, original order, only the fields in field_mask are written. */
+/* Device SoA -> host AoS, original order, only the fields in field_mask are written.  n may be smaller than
+ * sphb_count: the first n particles of the original order are returned. */
 int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask);
 
 /* --- the five public methods of SphUtils (SPH/SphUtils.hpp:40-44), on the device-resident state ---- */
@@ -169,8 +170,45 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
 /* Current device pointers (sorted order, valid until the next call that steps or uploads):
  * posm float4, vel float4, aux float4 (density, pressure, sqrt|P/rho|, 1/rho), accel float4, ids int32. */
 int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, void** accel, int32_t** ids);
+/* Copy the current state to host arrays in SORTED order (sphb_count records each; any pointer may be NULL):
+ * posm/vel/aux/accel 4 floats per particle, ids int32.  Synchronises. */
+int sphb_download_soa(sphb_engine* e, float* posm, float* vel, float* aux, float* accel, int32_t* ids);
 /* The CUDA stream (cudaStream_t) all of this engine's work is enqueued on. */
 void* sphb_stream(sphb_engine* e);
+
+/* --- multi-GPU: x-slab decomposition, one engine (one process) per GPU ------------------------------- */
+/* Nothing like this exists in the reference (single thread).  Each rank owns the particles
+ * whose x lies in [lo, hi) and keeps a ghost layer of width `halo` (2 support radii, so that ghost densities
+ * can be recomputed locally and ONE exchange per step suffices) copied from its two x-neighbours.  Ownership
+ * is carried in vel.w (1 = owned, 0 = ghost).  Per step:
+ *     sphb_mg_pack  ->  exchange the two messages with the neighbours (NCCL send/recv, or peer copies)
+ *                   ->  sphb_mg_unpack  ->  sphb_step(e, 1)
+ * A message is (capacity + 1) records of 32 bytes: a header {int32 count, int32 capacity, ...} and then
+ * {float4 posm, float4 vel} per particle, all in device memory owned by the caller. */
+typedef struct sphb_slab {
+    float lo, hi;             /* owned x-interval [lo, hi); use -INFINITY / +INFINITY at the ends of the domain */
+    float halo;               /* ghost width; >= 2*h*h for the single-exchange scheme */
+    int32_t has_left, has_right;
+    float shift_left, shift_right; /* added to x of records sent that way: +-period across a periodic seam, else 0 */
+} sphb_slab;
+
+/* Bytes of a message buffer that can carry `capacity` particles. */
+size_t sphb_mg_message_bytes(size_t capacity);
+
+/* Make room for up to n_max particles (owned + ghosts) before the first upload, so that the arrays need not
+ * grow when neighbours send more than this rank started with. */
+int sphb_reserve(sphb_engine* e, size_t n_max);
+
+/* Classify the particles this rank owned by their current x: the ones it keeps (as owned or as ghosts) are
+ * compacted into the engine's spare buffers, the ones a neighbour needs (its ghost zone, and migrants) into
+ * msg_left / msg_right (either may be NULL when that neighbour does not exist).  Previous ghosts are dropped.
+ * Deterministic (order-preserving compaction).  Asynchronous on the engine's stream. */
+int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* msg_right, size_t capacity);
+
+/* Append what the neighbours sent (NULL = none), refresh the ownership flags and adopt the new particle
+ * set.  Synchronises once to read the counts.  counts[4] (may be NULL) = {kept, from_left, from_right, total}.
+ * SPHB_ERR_CAPACITY if a sender overflowed its message or the arrays reserved with sphb_reserve are full. */
+int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, size_t counts[4]);
 
 /* --- allocation-free bounding box ------------------------------------------------------------------ */
 

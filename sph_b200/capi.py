@@ -32,6 +32,13 @@ class SphbError(RuntimeError):
     pass
 
 
+class Slab(C.Structure):
+    """struct sphb_slab (include/sphb200.h)."""
+
+    _fields_ = [("lo", C.c_float), ("hi", C.c_float), ("halo", C.c_float), ("has_left", C.c_int32), ("has_right", C.c_int32),
+                ("shift_left", C.c_float), ("shift_right", C.c_float)]
+
+
 class Params(C.Structure):
     """struct sphb_params (include/sphb200.h)."""
 
@@ -53,7 +60,8 @@ EXPORTS = [
     "sphb_update_posvel", "sphb_collision", "sphb_step", "sphb_step_aos", "sphb_synchronize",
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
-    "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc",
+    "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
+    "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
 ]
 
 _lib = None
@@ -104,7 +112,13 @@ def load_library() -> C.CDLL:
     L.sphb_get_device_state.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     L.sphb_stream.argtypes = [vp]
     L.sphb_stream.restype = vp
+    L.sphb_download_soa.argtypes = [vp, vp, vp, vp, vp, vp]
     L.sphb_bbox_noalloc.argtypes = [vp, sz, vp, vp]
+    L.sphb_mg_message_bytes.argtypes = [sz]
+    L.sphb_mg_message_bytes.restype = sz
+    L.sphb_reserve.argtypes = [vp, sz]
+    L.sphb_mg_pack.argtypes = [vp, C.POINTER(Slab), vp, vp, sz]
+    L.sphb_mg_unpack.argtypes = [vp, C.POINTER(Slab), vp, vp, C.POINTER(sz * 4)]
     _lib = L
     return L
 
@@ -181,6 +195,17 @@ class Engine:
         self._check(self.lib.sphb_download_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize, mask))
         return particles
 
+    def download_first(self, particles: np.ndarray, mask: int = F_ALL):
+        """Download the first len(particles) particles of the original order (the rest may be ghosts)."""
+        return self.download(particles, mask)
+
+    def download_soa(self):
+        """(posm, vel, aux, accel, ids) of the current state in SORTED order."""
+        n = self.count()
+        arrs = [np.zeros((n, 4), np.float32) for _ in range(4)] + [np.zeros(n, np.int32)]
+        self._check(self.lib.sphb_download_soa(self.h, *[_ptr(a) for a in arrs]))
+        return tuple(arrs)
+
     def upload_ptr(self, ptr: int, n: int, stride: int = 52):
         self._check(self.lib.sphb_upload_aos(self.h, C.c_void_p(ptr), n, stride))
 
@@ -190,6 +215,20 @@ class Engine:
     def upload_soa_device(self, posm_ptr: int, vel_ptr: int, n: int, ids_ptr: int | None = None):
         self._check(self.lib.sphb_upload_soa_device(self.h, C.c_void_p(posm_ptr), C.c_void_p(vel_ptr),
                                                     C.c_void_p(ids_ptr) if ids_ptr else None, n))
+
+    # --- multi-GPU slab decomposition
+    def reserve(self, n_max: int):
+        self._check(self.lib.sphb_reserve(self.h, n_max))
+
+    def mg_pack(self, slab: Slab, msg_left: int | None, msg_right: int | None, capacity: int):
+        self._check(self.lib.sphb_mg_pack(self.h, C.byref(slab), C.c_void_p(msg_left) if msg_left else None,
+                                          C.c_void_p(msg_right) if msg_right else None, capacity))
+
+    def mg_unpack(self, slab: Slab, from_left: int | None, from_right: int | None):
+        counts = (C.c_size_t * 4)()
+        self._check(self.lib.sphb_mg_unpack(self.h, C.byref(slab), C.c_void_p(from_left) if from_left else None,
+                                            C.c_void_p(from_right) if from_right else None, C.byref(counts)))
+        return tuple(int(c) for c in counts)
 
     # --- the SphUtils methods
     def update_cells(self):

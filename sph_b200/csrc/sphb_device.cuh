@@ -664,7 +664,7 @@ __global__ void __launch_bounds__(kAosThreads) k_aos_to_soa(const float* __restr
     const float* r = s_rec + threadIdx.x * stride_w;
     const int i = base + threadIdx.x;
     posm[i] = make_float4(r[kOffPos], r[kOffPos + 1], r[kOffPos + 2], r[kOffMass]);
-    vel[i] = make_float4(r[kOffVel], r[kOffVel + 1], r[kOffVel + 2], 0.0f);
+    vel[i] = make_float4(r[kOffVel], r[kOffVel + 1], r[kOffVel + 2], 1.0f); // w = 1: owned by this engine (multi-GPU: 0 = ghost)
     const float rho = r[kOffRho], P = r[kOffP];
     aux[i] = make_float4(rho, P, sqrtf(fabsf(__fdiv_rn(P, rho))), __frcp_rn(rho));
     accel[i] = make_float4(r[kOffAcc], r[kOffAcc + 1], r[kOffAcc + 2], 0.0f);
@@ -716,6 +716,147 @@ __global__ void __launch_bounds__(256) k_cells_xyz(const GridDesc* __restrict__ 
 __global__ void __launch_bounds__(256) k_fill_iota(int* __restrict__ ids, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) ids[i] = i;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Multi-GPU x-slab decomposition (nothing like it in the reference, which is one thread).
+// After a step every rank classifies the particles it OWNED (vel.w != 0) by their new x:
+//   keep       x in [lo - halo, hi + halo): stays in this rank's arrays, owned if x in [lo, hi) else ghost
+//   to left    x <  lo + halo  (owned boundary layer of the left neighbour's ghost zone, and migrants)
+//   to right   x >= hi - halo
+// Ghosts of the previous step (vel.w == 0) are dropped: they are re-sent every step.  All three outputs are
+// compacted in input order with a two-level scan (per-block counts -> scan -> write), so the result is
+// deterministic.  A message is a header record {count, capacity, 0...} followed by 32-byte particle
+// records {posm float4, vel float4}; the receiver appends them and sets the ownership flag itself.
+
+struct Slab {
+    float lo, hi, halo;
+    int has_left, has_right;
+    float shift_left, shift_right; // added to x of a record sent that way (periodic seam), else 0
+};
+
+constexpr int kMgThreads = 256;
+
+__device__ __forceinline__ void mg_classify(const Slab& s, const float4& p, const float4& v, bool& keep, bool& left, bool& right) {
+    const bool owned = v.w != 0.0f;
+    const float x = p.x;
+    keep = owned && x >= s.lo - s.halo && x < s.hi + s.halo;
+    left = owned && s.has_left && x < s.lo + s.halo;
+    right = owned && s.has_right && x >= s.hi - s.halo;
+}
+
+// pass 1: per-block counts of (keep, left, right)
+__global__ void __launch_bounds__(kMgThreads) k_mg_count(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
+                                                         int* __restrict__ block_counts) {
+    const int i = blockIdx.x * kMgThreads + threadIdx.x;
+    bool keep = false, left = false, right = false;
+    if (i < n) mg_classify(s, posm[i], vel[i], keep, left, right);
+    const int ck = __syncthreads_count(keep), cl = __syncthreads_count(left), cr = __syncthreads_count(right);
+    if (threadIdx.x == 0) {
+        block_counts[3 * blockIdx.x] = ck;
+        block_counts[3 * blockIdx.x + 1] = cl;
+        block_counts[3 * blockIdx.x + 2] = cr;
+    }
+}
+
+// pass 2: one block turns the per-block counts into exclusive offsets (3 interleaved streams) and totals
+__global__ void __launch_bounds__(kMgThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int* __restrict__ totals) {
+    __shared__ int s_part[3][kMgThreads];
+    int carry[3] = {0, 0, 0};
+    for (int base = 0; base < nblocks; base += kMgThreads) {
+        const int b = base + threadIdx.x;
+        int v[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            v[k] = b < nblocks ? block_counts[3 * b + k] : 0;
+            s_part[k][threadIdx.x] = v[k];
+        }
+        __syncthreads();
+        // Hillis-Steele inclusive scan over the chunk, three streams at once
+        for (int o = 1; o < kMgThreads; o <<= 1) {
+            int t[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) t[k] = threadIdx.x >= o ? s_part[k][threadIdx.x - o] : 0;
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 3; k++) s_part[k][threadIdx.x] += t[k];
+            __syncthreads();
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            if (b < nblocks) block_counts[3 * b + k] = carry[k] + s_part[k][threadIdx.x] - v[k];
+            carry[k] += s_part[k][kMgThreads - 1];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x < 3) totals[threadIdx.x] = carry[threadIdx.x];
+}
+
+// pass 3: write.  keep -> (posm_out, vel_out) with the ownership flag refreshed; left/right -> messages.
+__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
+                                                         const int* __restrict__ block_offsets, const int* __restrict__ totals,
+                                                         float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                         float4* __restrict__ msg_left, float4* __restrict__ msg_right, int capacity) {
+    __shared__ int s_warp[3][kMgThreads / 32];
+    const int i = blockIdx.x * kMgThreads + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    bool f[3] = {false, false, false};
+    float4 p = make_float4(0, 0, 0, 0), v = p;
+    if (i < n) {
+        p = posm[i];
+        v = vel[i];
+        mg_classify(s, p, v, f[0], f[1], f[2]);
+    }
+    int rank[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const unsigned b = __ballot_sync(0xffffffffu, f[k]);
+        rank[k] = __popc(b & ((1u << lane) - 1));
+        if (lane == 0) s_warp[k][warp] = __popc(b);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        int off = block_offsets[3 * blockIdx.x + k];
+        for (int w = 0; w < warp; w++) off += s_warp[k][w];
+        rank[k] += off;
+    }
+    if (f[0]) {
+        const bool inside = p.x >= s.lo && p.x < s.hi;
+        posm_out[rank[0]] = p;
+        vel_out[rank[0]] = make_float4(v.x, v.y, v.z, inside ? 1.0f : 0.0f);
+    }
+    if (f[1] && rank[1] < capacity) {
+        msg_left[2 + 2 * rank[1]] = make_float4(p.x + s.shift_left, p.y, p.z, p.w);
+        msg_left[3 + 2 * rank[1]] = v;
+    }
+    if (f[2] && rank[2] < capacity) {
+        msg_right[2 + 2 * rank[2]] = make_float4(p.x + s.shift_right, p.y, p.z, p.w);
+        msg_right[3 + 2 * rank[2]] = v;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { // headers: count, capacity
+        if (msg_left) msg_left[0] = make_float4(__int_as_float(s.has_left ? totals[1] : 0), __int_as_float(capacity), 0.0f, 0.0f);
+        if (msg_right) msg_right[0] = make_float4(__int_as_float(s.has_right ? totals[2] : 0), __int_as_float(capacity), 0.0f, 0.0f);
+    }
+}
+
+// append a received message behind the kept particles; counts[0] = kept, counts[1] = records already appended
+__global__ void __launch_bounds__(256) k_mg_append(Slab s, const float4* __restrict__ msg, const int* __restrict__ totals, int which,
+                                                   float4* __restrict__ posm_out, float4* __restrict__ vel_out, int out_capacity,
+                                                   int* __restrict__ recv_counts) {
+    const int count = min(__float_as_int(msg[0].x), __float_as_int(msg[0].y)); // an overflowing sender truncated its payload
+    const int base = totals[0] + (which ? recv_counts[0] : 0);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        recv_counts[which] = count;
+        recv_counts[2 + which] = __float_as_int(msg[0].x); // what the sender wanted to send (overflow check)
+    }
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < count; r += gridDim.x * blockDim.x) {
+        if (base + r >= out_capacity) break;
+        const float4 p = msg[2 + 2 * r], v = msg[3 + 2 * r];
+        const bool inside = p.x >= s.lo && p.x < s.hi;
+        posm_out[base + r] = p;
+        vel_out[base + r] = make_float4(v.x, v.y, v.z, inside ? 1.0f : 0.0f);
+    }
 }
 
 } // namespace sphb

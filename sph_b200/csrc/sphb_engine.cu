@@ -73,6 +73,10 @@ struct sphb_engine {
     DevBuf<int> block_sums;
     DevBuf<float> aos;      // staging for host AoS records
     DevBuf<float> scratch;  // eval_kernels, cells download
+    DevBuf<int> mg_counts;  // multi-GPU pack: 3 per block, then totals[3] and recv_counts[4]
+    int mg_blocks = 0;
+    bool mg_pending = false; // sphb_mg_pack ran, sphb_mg_unpack has not committed yet
+    size_t reserved = 0;
     GridDesc* d_grid = nullptr;
     BBoxAcc* d_bbox = nullptr;
     long long max_cells = 0;
@@ -138,7 +142,8 @@ void build_consts(sphb_engine* e) {
 }
 
 int ensure_capacity(sphb_engine* e, size_t n) {
-    const size_t want = n ? n : 1;
+    size_t want = n ? n : 1;
+    if (want < e->reserved) want = e->reserved;
     for (int b = 0; b < 2; b++) {
         CK(e->posm[b].reserve(want));
         CK(e->vel[b].reserve(want));
@@ -299,7 +304,7 @@ void sphb_destroy(sphb_engine* e) {
         e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
     }
     e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release();
-    e->cell_start.release(); e->block_sums.release(); e->aos.release(); e->scratch.release();
+    e->cell_start.release(); e->block_sums.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release();
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
     if (e->ev) {
@@ -387,7 +392,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
 int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask) {
     int rc = check_ready(e);
     if (rc) return rc;
-    if (n != e->n) return fail(SPHB_ERR_INVALID, "download of %zu particles but the engine holds %zu", n, e->n);
+    if (n > e->n) return fail(SPHB_ERR_INVALID, "download of %zu particles but the engine holds %zu", n, e->n);
     if (n && !particles) return fail(SPHB_ERR_INVALID, "null particles");
     if (stride < 48 || stride % 4 || stride > 128) return fail(SPHB_ERR_INVALID, "stride must be a multiple of 4 in [48, 128]");
     if (n == 0) return SPHB_OK;
@@ -400,7 +405,7 @@ int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, 
         e->aos_valid = true;
     }
     const int cur = e->cur;
-    LAUNCH(e, k_invert_perm, cdiv(n, 256), 256, 0, e->oid[cur].p, e->inv.p, (int)n);
+    LAUNCH(e, k_invert_perm, cdiv(e->n, 256), 256, 0, e->oid[cur].p, e->inv.p, (int)e->n);
     LAUNCH(e, k_soa_to_aos, cdiv(n, kAosThreads), kAosThreads, kAosThreads * stride, e->aos.p, (int)sw, (int)n, e->inv.p, e->posm[cur].p,
            e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, field_mask);
     CK(cudaGetLastError());
@@ -647,9 +652,102 @@ int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, v
     return SPHB_OK;
 }
 
+int sphb_download_soa(sphb_engine* e, float* posm, float* vel, float* aux, float* accel, int32_t* ids) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    const size_t n = e->n;
+    const int cur = e->cur;
+    if (n) {
+        if (posm) CK(cudaMemcpyAsync(posm, e->posm[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
+        if (vel) CK(cudaMemcpyAsync(vel, e->vel[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
+        if (aux) CK(cudaMemcpyAsync(aux, e->aux[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
+        if (accel) CK(cudaMemcpyAsync(accel, e->accel[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
+        if (ids) CK(cudaMemcpyAsync(ids, e->oid[cur].p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    return SPHB_OK;
+}
+
 void* sphb_stream(sphb_engine* e) { return e ? (void*)e->stream : nullptr; }
 
 } // extern "C"
+
+// =====================================================================================================
+// Multi-GPU slab decomposition (include/sphb200.h: sphb_mg_*)
+
+extern "C" size_t sphb_mg_message_bytes(size_t capacity) { return (capacity + 1) * 2 * sizeof(float4); }
+
+extern "C" int sphb_reserve(sphb_engine* e, size_t n_max) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (e->have_state && n_max > e->posm[0].cap) return fail(SPHB_ERR_STATE, "sphb_reserve must come before the first upload");
+    if (n_max > 0x7fffff00u) return fail(SPHB_ERR_CAPACITY, "too many particles");
+    int rc = use_device(e);
+    if (rc) return rc;
+    e->reserved = n_max;
+    return ensure_capacity(e, n_max);
+}
+
+extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* msg_right, size_t capacity) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
+    if ((slab->has_left && !msg_left) || (slab->has_right && !msg_right)) return fail(SPHB_ERR_INVALID, "missing message buffer");
+    if (capacity > 0x3fffffffu) return fail(SPHB_ERR_CAPACITY, "message capacity too large");
+    Slab s;
+    s.lo = slab->lo; s.hi = slab->hi; s.halo = slab->halo;
+    s.has_left = slab->has_left; s.has_right = slab->has_right;
+    s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
+    const int n = (int)e->n, cur = e->cur, nxt = cur ^ 1;
+    const int nb = n ? cdiv(n, kMgThreads) : 1;
+    CK(e->mg_counts.reserve((size_t)3 * nb + 16));
+    e->mg_blocks = nb;
+    int* totals = e->mg_counts.p + 3 * nb;
+    LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p);
+    LAUNCH(e, k_mg_scan, 1, kMgThreads, 0, e->mg_counts.p, nb, totals);
+    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, e->posm[nxt].p,
+           e->vel[nxt].p, (float4*)msg_left, (float4*)msg_right, (int)capacity);
+    CK(cudaGetLastError());
+    e->mg_pending = true;
+    return SPHB_OK;
+}
+
+extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, size_t counts[4]) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
+    if (!e->mg_pending) return fail(SPHB_ERR_STATE, "sphb_mg_unpack without sphb_mg_pack");
+    Slab s;
+    s.lo = slab->lo; s.hi = slab->hi; s.halo = slab->halo;
+    s.has_left = slab->has_left; s.has_right = slab->has_right;
+    s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
+    const int nxt = e->cur ^ 1;
+    int* totals = e->mg_counts.p + 3 * e->mg_blocks;
+    int* recv = totals + 4;
+    const int cap = (int)(e->posm[nxt].cap < 0x7fffffffu ? e->posm[nxt].cap : 0x7fffffffu);
+    CK(cudaMemsetAsync(recv, 0, 4 * sizeof(int), e->stream));
+    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[nxt].p, e->vel[nxt].p, cap, recv);
+    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[nxt].p, e->vel[nxt].p, cap, recv);
+    CK(cudaGetLastError());
+    int h[8];
+    CK(cudaMemcpyAsync(h, totals, 8 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    const long long kept = h[0], cl = h[4], cr = h[5], total = kept + cl + cr;
+    e->mg_pending = false;
+    if (h[6] > cl || h[7] > cr) return fail(SPHB_ERR_CAPACITY, "a neighbour overflowed its message (wanted %d / %d records)", h[6], h[7]);
+    if (total > cap) return fail(SPHB_ERR_CAPACITY, "%lld particles exceed the reserved %d: call sphb_reserve with more room", total, cap);
+    e->cur = nxt;
+    e->n = (size_t)total;
+    if (total) {
+        LAUNCH(e, k_fill_iota, cdiv(total, 256), 256, 0, e->oid[nxt].p, (int)total);
+        CK(cudaGetLastError());
+    }
+    e->grid_valid = false;
+    e->mask_valid = false;
+    e->bbox_valid = false;
+    e->aos_valid = false;
+    if (counts) { counts[0] = (size_t)kept; counts[1] = (size_t)cl; counts[2] = (size_t)cr; counts[3] = (size_t)total; }
+    return SPHB_OK;
+}
 
 // =====================================================================================================
 // Allocation-free bounding box (include/sphb200.h: sphb_bbox_noalloc).  Self-contained: it shares no

@@ -1,0 +1,263 @@
+"""Multi-GPU driver: x-slab domain decomposition, one process (one engine) per GPU.
+
+Nothing like this exists in the reference (one thread).  Each rank owns the particles with
+x in [lo, hi) and mirrors a ghost layer of 2 support radii from its two x-neighbours, so that ghost
+densities are recomputed locally and ONE exchange per step suffices:
+
+    engine.mg_pack(slab, msg_left, msg_right)      # CUDA: classify + deterministic compaction (libsphb200)
+    exchange(...)                                  # torch.distributed point-to-point (NCCL over NVLink)
+    engine.mg_unpack(slab, from_left, from_right)  # CUDA: append, refresh ownership flags, adopt
+    engine.step(1)                                 # sort + density + fused force/integrate/collide
+
+There is no collective on the data path: only the two neighbour messages.  torch is plumbing here (device
+buffers for the messages, the process group); every particle operation is a kernel behind the C ABI.
+"""
+from __future__ import annotations
+
+import math
+import os
+
+import numpy as np
+
+from . import capi
+
+RECORD = 32  # bytes per particle in a message: float4 posm + float4 vel
+
+
+def support_radius(h=0.45) -> float:
+    return float(np.float32(h) * np.float32(h))
+
+
+def make_slab(rank: int, world: int, bounds, halo: float, period: float | None = None) -> capi.Slab:
+    """bounds: world+1 increasing x values; the outer two are replaced by -inf/+inf unless periodic."""
+    s = capi.Slab()
+    periodic = period is not None
+    s.lo = float(bounds[rank]) if (rank > 0 or periodic) else -math.inf
+    s.hi = float(bounds[rank + 1]) if (rank < world - 1 or periodic) else math.inf
+    s.halo = float(halo)
+    s.has_left = int(rank > 0 or (periodic and world > 1))
+    s.has_right = int(rank < world - 1 or (periodic and world > 1))
+    s.shift_left = float(period) if (periodic and rank == 0) else 0.0
+    s.shift_right = -float(period) if (periodic and rank == world - 1) else 0.0
+    return s
+
+
+def neighbours(rank: int, world: int, periodic: bool = False):
+    left = rank - 1 if rank > 0 else (world - 1 if periodic and world > 1 else None)
+    right = rank + 1 if rank < world - 1 else (0 if periodic and world > 1 else None)
+    return left, right
+
+
+def quantile_bounds(x: np.ndarray, world: int, cell: float, lo: float, hi: float):
+    """Slab boundaries at particle-count quantiles of x, snapped to multiples of `cell`."""
+    qs = np.quantile(x, np.linspace(0, 1, world + 1)[1:-1]) if world > 1 else []
+    inner = [lo + round((q - lo) / cell) * cell for q in qs]
+    return [lo] + inner + [hi]
+
+
+def exchange(dist, send_left, send_right, recv_left, recv_right, left, right):
+    """Post the (at most) four point-to-point operations of one halo exchange and wait for them.
+    Works on any backend (NCCL on device tensors, gloo on CPU tensors in the tests)."""
+    ops = []
+    if right is not None:
+        ops.append(dist.P2POp(dist.isend, send_right, right))
+    if left is not None:
+        ops.append(dist.P2POp(dist.irecv, recv_left, left))
+    if left is not None:
+        ops.append(dist.P2POp(dist.isend, send_left, left))
+    if right is not None:
+        ops.append(dist.P2POp(dist.irecv, recv_right, right))
+    if not ops:
+        return
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+
+
+class SlabRank:
+    """One rank's engine plus its message buffers."""
+
+    def __init__(self, engine: capi.Engine, slab: capi.Slab, capacity: int, device_index: int):
+        import torch
+        self.torch = torch
+        self.engine = engine
+        self.slab = slab
+        self.capacity = int(capacity)
+        nbytes = int(engine.lib.sphb_mg_message_bytes(self.capacity))
+        dev = torch.device("cuda", device_index)
+        mk = lambda: torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        self.send_left, self.send_right, self.recv_left, self.recv_right = mk(), mk(), mk(), mk()
+        self.stream = torch.cuda.ExternalStream(engine.stream(), device=dev)
+        self.counts = (0, 0, 0, 0)
+
+    def pack(self):
+        s = self.slab
+        self.engine.mg_pack(s, self.send_left.data_ptr() if s.has_left else None,
+                            self.send_right.data_ptr() if s.has_right else None, self.capacity)
+
+    def unpack(self):
+        s = self.slab
+        self.counts = self.engine.mg_unpack(s, self.recv_left.data_ptr() if s.has_left else None,
+                                            self.recv_right.data_ptr() if s.has_right else None)
+        return self.counts
+
+    def exchange_distributed(self, dist, left, right):
+        # NCCL enqueues after the current stream: make that the engine's stream so pack -> send and recv -> unpack order
+        with self.torch.cuda.stream(self.stream):
+            exchange(dist, self.send_left, self.send_right, self.recv_left, self.recv_right, left, right)
+
+    def step(self, dist=None, left=None, right=None):
+        self.pack()
+        if dist is not None:
+            self.exchange_distributed(dist, left, right)
+        self.unpack()
+        self.engine.step(1)
+
+    def owned(self):
+        """(posm, vel) of the owned particles in sorted order, as numpy arrays (diagnostics / tests)."""
+        posm, vel = self.engine.download_soa()[:2]
+        keep = vel[:, 3] != 0
+        return posm[keep], vel[keep]
+
+
+def exchange_in_process(ranks, periodic=False):
+    """Emulates the neighbour exchange for several SlabRanks living in ONE process on one GPU (tests on a
+    single-GPU box): the send buffers are copied into the neighbours' receive buffers."""
+    world = len(ranks)
+    for r in ranks:
+        r.engine.synchronize()
+    for i, r in enumerate(ranks):
+        left, right = neighbours(i, world, periodic)
+        if right is not None:
+            ranks[right].recv_left.copy_(r.send_right)
+        if left is not None:
+            ranks[left].recv_right.copy_(r.send_left)
+    ranks[0].torch.cuda.synchronize()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# bench.py --gpus N (launched under torchrun): weak scaling, one block-drop tank section per GPU
+
+def bench_main(args, world, rank, local):
+    import json
+    import time
+
+    import torch
+    import torch.distributed as dist
+
+    import bench as B
+    from . import scenes
+
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    scale = {"drop16m": 1, "drop2m": 2, "drop256k": 4}.get(args.workload)
+    if scale is None:
+        raise SystemExit("multi-GPU bench runs the block-drop workloads (drop16m / drop2m / drop256k)")
+    section = 256 // scale * 0.1                     # x-length of one tank section = one GPU's share
+    ps = scenes.block_drop_section(rank, world, scale=scale)
+    walls = scenes.tank_walls(section * world + 0.2, section + 0.2)
+    n_own = len(ps)
+    R = support_radius()
+    halo = 2.0 * R * 1.001
+    bounds = [0.1 + section * r for r in range(world + 1)]
+    slab = make_slab(rank, world, bounds, halo)
+    left, right = neighbours(rank, world)
+    top = 0.1 + (192 + 256) // scale * 0.1 + 0.3 + 1.0
+    dlo = (bounds[rank] - halo - 0.35, -0.25, -0.25)
+    dhi = (bounds[rank + 1] + halo + 0.35, top, section + 0.45)
+    eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi,
+                      write_accel=0 if args.no_accel else 1)
+    eng.set_walls(walls)
+    face = (section + 0.2) * (192 // scale * 0.1 + 0.5) * 1100.0      # particles per unit x near a face (upper bound)
+    capacity = int(face * halo * 2.0) + 4096
+    eng.reserve(n_own + 2 * capacity)
+    sr = SlabRank(eng, slab, capacity, local)
+
+    host = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
+    host_np = host.numpy().view(capi.PARTICLE)
+    host_np[:] = ps
+    del ps
+    eng.upload(host_np)
+
+    def one_step():
+        sr.step(dist, left, right)
+
+    for _ in range(max(3, args.warmup)):
+        one_step()
+    eng.synchronize()
+    launches0 = eng.launch_count()
+    eng.enable_timing(True)
+    sampler = B.ClockSampler(local) if rank == 0 else None
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dist.barrier()
+    torch.cuda.synchronize()
+    start.record(sr.stream)
+    for _ in range(args.steps):
+        one_step()
+    stop.record(sr.stream)
+    eng.synchronize()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = torch.tensor([start.elapsed_time(stop)], device="cuda")
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clocks = sampler.stop() if sampler else None
+    launches = eng.launch_count() - launches0
+    phase, timed = eng.get_timing()
+    eng.enable_timing(False)
+    _, vel = sr.owned()
+    owned = torch.tensor([len(vel)], device="cuda", dtype=torch.int64)
+    dist.all_reduce(owned)
+    total = int(owned.item())
+    value = total * args.steps / (ms * 1e-3)
+
+    # end to end on host records: upload own records, exchange ghosts, step, download own records
+    e2e_steps = max(1, args.e2e_steps)
+    out = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
+    out_np = out.numpy().view(capi.PARTICLE)
+
+    def e2e_step():
+        eng.upload(host_np)             # the rank's own 52-byte records (pinned)
+        sr.step(dist, left, right)      # ghosts come from the neighbours
+        eng.download_first(out_np)      # own records back (ghosts are not returned)
+
+    e2e_step()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    t = torch.tensor([(time.perf_counter() - t0) / e2e_steps], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t_e2e = float(t.item())
+
+    if rank == 0:
+        peak, peak_src = B.measured_peak()
+        bforce = B.B_FORCE_NOACC if args.no_accel else B.B_FORCE
+        n_local = eng.count()
+        ach = bforce * n_local / (float(phase[2]) * 1e-3) / 1e9
+        line = {
+            "metric": B.METRIC, "value": value, "unit": B.UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": B.WORKLOADS[args.workload] + f", one tank section per GPU ({world} sections side by side)",
+                       "particles": total, "particles_per_gpu": n_own, "decomposition": "x slabs, halo = 2 support radii, "
+                       "one NCCL send/recv pair per neighbour per step", "l2": "state exceeds the 126 MB L2",
+                       "accel_output": not args.no_accel},
+            "clocks": clocks,
+            "e2e": {"value": total / t_e2e, "unit": B.UNIT, "h2d_bytes_per_step": n_own * 52 * world, "d2h_bytes_per_step": n_own * 52 * world,
+                    "ms_per_step": 1e3 * t_e2e, "call": "per rank: sphb_upload_aos + halo exchange + sphb_step + sphb_download_aos"},
+            "gpu_launches": int(launches) * world,
+            "roofline": {"bound": "hbm", "kernel": "k_force (rank 0)", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": None, "peak_source": peak_src, "bytes_per_particle": bforce, "kernel_ms": float(phase[2]),
+                         "local_particles_incl_ghosts": n_local, "steps_averaged": int(timed)},
+            "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "engine_step": float(phase[3]),
+                         "exchange_and_pack": ms / args.steps - float(phase[3])},
+            "halo": {"counts_rank0": {"kept": sr.counts[0], "from_left": sr.counts[1], "from_right": sr.counts[2]},
+                     "message_capacity": capacity},
+            "cpu_baseline": None,
+        }
+        print(json.dumps(line, default=float), flush=True)
+    eng.close()
+    dist.barrier()
+    dist.destroy_process_group()

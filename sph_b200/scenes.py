@@ -162,3 +162,20 @@ def block_drop(scale=1, seed=1234):
     vel = np.concatenate([pool_vel, blk_vel])
     t = px * s + 0.2
     return make_particles(pos, vel), tank_walls(t, t)
+
+
+def block_drop_section(rank, world, scale=1, seed=1234):
+    """Weak-scaling variant of block_drop: `world` tank sections of x-length 25.6/scale side by side in one long
+    tank, each with the pool + falling block pattern of config 4; returns the particles of section `rank`
+    (positions in GLOBAL coordinates).  rank=0, world=1 is block_drop(scale) itself."""
+    px, py, pz = 256 // scale, 192 // scale, 256 // scale
+    bx, by, bz = 128 // scale, 256 // scale, 128 // scale
+    s = 0.1
+    per = px * py * pz + bx * by * bz
+    x0 = px * s * rank
+    pool_pos, pool_vel = lattice_block(px, py, pz, s, (0.1 + x0, 0.1, 0.1), seed=seed, jitter=0.2, index0=per * rank)
+    top = 0.1 + py * s + 0.3
+    off = 0.1 + (px - bx) * s / 2
+    blk_pos, blk_vel = lattice_block(bx, by, bz, s, (off + x0, top, off), seed=seed, jitter=0.2, index0=per * rank + px * py * pz)
+    blk_vel[:, 1] = -1.0
+    return make_particles(np.concatenate([pool_pos, blk_pos]), np.concatenate([pool_vel, blk_vel]))

@@ -1,0 +1,84 @@
+"""Host-side logic of the multi-GPU slab decomposition, on CPU: slab/neighbour tables and the point-to-point
+exchange protocol under torch.distributed with the gloo backend, world sizes 2 and 3 (the same function that
+runs over NCCL on the GPUs).  The CUDA pack/unpack kernels are covered by tests/test_gpu_multirank.py."""
+import math
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from sph_b200 import multigpu
+
+
+def test_slab_tables():
+    bounds = [0.0, 1.0, 2.5, 4.0]
+    s0, s1, s2 = (multigpu.make_slab(r, 3, bounds, 0.4) for r in range(3))
+    assert (s0.lo, s0.hi, s0.has_left, s0.has_right) == (-math.inf, 1.0, 0, 1)
+    assert (s1.lo, s1.hi, s1.has_left, s1.has_right) == (1.0, 2.5, 1, 1)
+    assert (s2.lo, s2.hi, s2.has_left, s2.has_right) == (2.5, math.inf, 1, 0)
+    assert s0.shift_left == s0.shift_right == s2.shift_right == 0.0
+    p0, p2 = multigpu.make_slab(0, 3, bounds, 0.4, period=4.0), multigpu.make_slab(2, 3, bounds, 0.4, period=4.0)
+    assert (p0.lo, p0.has_left, p0.shift_left) == (0.0, 1, 4.0)          # records leaving rank 0 leftwards reappear at x + L
+    assert (p2.hi, p2.has_right, p2.shift_right) == (4.0, 1, -4.0)
+    assert multigpu.neighbours(0, 3) == (None, 1) and multigpu.neighbours(2, 3) == (1, None)
+    assert multigpu.neighbours(0, 3, periodic=True) == (2, 1) and multigpu.neighbours(2, 3, periodic=True) == (1, 0)
+    assert multigpu.neighbours(0, 1, periodic=True) == (None, None)
+    one = multigpu.make_slab(0, 1, [0.0, 4.0], 0.4)
+    assert (one.lo, one.hi, one.has_left, one.has_right) == (-math.inf, math.inf, 0, 0)
+
+
+def test_quantile_bounds_balance():
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.uniform(0, 1, 30000), rng.uniform(0, 4, 10000)])     # dam-break-like: dense on the left
+    b = multigpu.quantile_bounds(x, 4, 0.2025, 0.0, 4.0)
+    assert b[0] == 0.0 and b[-1] == 4.0 and all(b[i] < b[i + 1] for i in range(4))
+    counts = np.histogram(x, b)[0]
+    assert counts.max() / counts.min() < 2.2      # snapping to a cell plane costs up to half a cell of particles
+    assert all(abs((v / 0.2025) - round(v / 0.2025)) < 1e-9 for v in b[1:-1])       # snapped to cell planes
+
+
+def _worker(rank, world, port, periodic, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        left, right = multigpu.neighbours(rank, world, periodic)
+        n = 64
+        send_left = torch.full((n,), float(10 * rank + 1))
+        send_right = torch.full((n,), float(10 * rank + 2))
+        recv_left, recv_right = torch.full((n,), -1.0), torch.full((n,), -1.0)
+        for _ in range(3):      # several steps in a row: matching must stay in lock-step
+            multigpu.exchange(dist, send_left, send_right, recv_left, recv_right, left, right)
+        q.put((rank, left, right, float(recv_left[0]), float(recv_right[-1])))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("world,periodic", [(2, False), (3, False), (3, True), (2, True)])
+def test_exchange_protocol_gloo(world, periodic):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, periodic, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(world):
+        rank, left, right, from_left, from_right = q.get(timeout=120)
+        got[rank] = (left, right, from_left, from_right)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, (left, right, from_left, from_right) in got.items():
+        # what arrives from the left neighbour is what it sent to ITS right, and vice versa
+        assert from_left == (10 * left + 2 if left is not None else -1.0)
+        assert from_right == (10 * right + 1 if right is not None else -1.0)
