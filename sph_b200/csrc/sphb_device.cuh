@@ -80,6 +80,19 @@ __device__ __forceinline__ float fast_rcp(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+__device__ __forceinline__ float fast_sqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// aux record (rho, P, sqrt|P/rho|, 1/rho).  The last two are helpers of the pair body (SphUtils.cpp:223,228),
+// never returned to the host; they are computed by this ONE function wherever they are needed (density
+// kernel, upload, per-neighbour re-derivation) so that every path sees the same bits.
+__device__ __forceinline__ float4 make_aux(float rho, float P) {
+    const float inv = fast_rcp(rho);
+    return make_float4(rho, P, fast_sqrt(fabsf(P * inv)), inv);
+}
 
 // Cell coordinate along one axis.  Same expression as SphUtils.cpp:38-40, floor((p - min) / cell), in
 // IEEE float (no FMA, true division), then clamped to the grid so that strays stay adjacent to their
@@ -382,21 +395,20 @@ constexpr int kMaskBits = 64;
 
 // ---------------------------------------------------------------------------------------------------
 // K4: density + equation of state (SphUtils.cpp:100-149) + neighbour masks.  One thread per sorted
-// particle.  aux = (rho, P, sqrt|P/rho|, 1/rho): the last two are precomputed for the force kernel
-// (SphUtils.cpp:223 evaluates sqrt|P/rho| per pair).
+// particle.  aux = (rho, P, sqrt|P/rho|, 1/rho) (SphUtils.cpp:223 evaluates sqrt|P/rho| per pair).
 
 __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
     float rho = sum * c.Kw;
     if (rho < c.rho0) rho = c.rho0;                 // SphUtils.cpp:141-142 (clamp UP)
     float P = __fmul_rn(c.eos_k, __fsub_rn(rho, c.rho0)); // :144
-    float inv = __frcp_rn(rho);
-    return make_float4(rho, P, sqrtf(fabsf(__fdiv_rn(P, rho))), inv);
+    return make_aux(rho, P);
 }
 
 // kAux: compute and store density/pressure.  kMask: store the neighbour masks.
 template <bool kAux, bool kMask>
 __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
-                                                 const float4* __restrict__ posm, float4* __restrict__ aux,
+                                                 const float4* __restrict__ posm, const float4* __restrict__ vel,
+                                                 float4* __restrict__ aux, float4* __restrict__ vr,
                                                  unsigned int* __restrict__ mask, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -450,7 +462,13 @@ __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __res
     if (kAux) {
         // self term: every run above included j == i exactly once (its own cell's row); take it out again
         sum -= pi.w * (c.h2 * c.h2 * c.h2);
-        aux[i] = finish_density(c, sum);
+        const float4 a = finish_density(c, sum);
+        aux[i] = a;
+        // the force kernel gathers two records per neighbour: posm and (vx, vy, vz, rho); P, sqrt|P/rho| and
+        // 1/rho are functions of rho and are recomputed there (two gathers instead of three: the kernel is
+        // bound by L1 gather wavefronts, profiles/r1b)
+        const float4 v = ldg4(vel + i);
+        vr[i] = make_float4(v.x, v.y, v.z, a.x);
     }
 }
 
@@ -478,6 +496,12 @@ __device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, 
     ax = fmaf(wgt, dx, ax);
     ay = fmaf(wgt, dy, ay);
     az = fmaf(wgt, dz, az);
+}
+
+// The neighbour's (P, sqrt|P/rho|, 1/rho) from its rho alone, as finish_density computes them (P with the
+// same rounding; the other two through MUFU approximations, <= 2 ulp).
+__device__ __forceinline__ float4 aux_from_rho(const Consts& c, float rho) {
+    return make_aux(rho, __fmul_rn(c.eos_k, __fsub_rn(rho, c.rho0)));
 }
 
 // SphUtils.cpp:326-328 with the reference's rounding (mul then add, no FMA): bit-exact given equal accel
@@ -520,10 +544,13 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
 // across the rows, so the lanes of a warp stay together on the pair body however the neighbours are
 // spread over the rows.  Masks and run starts are staged per thread in shared memory (column tid: no
 // conflicts, no barrier needed).
-template <bool kFused, bool kBBox, bool kAccel, int kRows>
+// kDerive: gather (vx,vy,vz,rho) records written by k_density and derive P etc. from rho (two gathers per
+//          neighbour); otherwise gather vel and aux separately (three; needed when rho/P were uploaded and P
+//          need not equal k(rho - rho0)).
+template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive>
 __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
-                                               const unsigned int* __restrict__ mask,
+                                               const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
                                                float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                BBoxAcc* bbox, int n) {
     __shared__ unsigned int s_mask[2 * kRows][128];
@@ -561,8 +588,14 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             const int j = jb + __ffs((int)m) - 1;
             m &= m - 1;
             const float4 pj = ldg4(posm + j);
-            const float4 vj = ldg4(vel + j);
-            const float4 aj = ldg4(aux + j);
+            float4 vj, aj;
+            if (kDerive) {
+                vj = ldg4(vr + j);
+                aj = aux_from_rho(c, vj.w);
+            } else {
+                vj = ldg4(vel + j);
+                aj = ldg4(aux + j);
+            }
             const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
             const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
             pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, vj, aj, ax, ay, az);
@@ -666,7 +699,7 @@ __global__ void __launch_bounds__(kAosThreads) k_aos_to_soa(const float* __restr
     posm[i] = make_float4(r[kOffPos], r[kOffPos + 1], r[kOffPos + 2], r[kOffMass]);
     vel[i] = make_float4(r[kOffVel], r[kOffVel + 1], r[kOffVel + 2], 1.0f); // w = 1: owned by this engine (multi-GPU: 0 = ghost)
     const float rho = r[kOffRho], P = r[kOffP];
-    aux[i] = make_float4(rho, P, sqrtf(fabsf(__fdiv_rn(P, rho))), __frcp_rn(rho));
+    aux[i] = make_aux(rho, P);
     accel[i] = make_float4(r[kOffAcc], r[kOffAcc + 1], r[kOffAcc + 2], 0.0f);
     oid[i] = i;
 }

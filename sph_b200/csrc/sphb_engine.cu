@@ -68,6 +68,8 @@ struct sphb_engine {
     DevBuf<int> key, slot, inv;
     DevBuf<int2> pairs;
     DevBuf<unsigned int> mask;       // neighbour masks, 2 words x rows x n
+    DevBuf<float4> vr;               // (vx, vy, vz, rho) in sorted order, written by k_density for k_force's gathers
+    bool vr_valid = false;           // vr matches the current sorted state and aux came from k_density
     int rows = 9;                    // (2*stencil+1)^2
     DevBuf<int> cell_start; // max_cells + 1 (+ slack)
     DevBuf<int> block_sums;
@@ -157,6 +159,7 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     CK(e->pairs.reserve(want));
     e->rows = (e->c.cell >= e->c.h2) ? 9 : 25;
     CK(e->mask.reserve(want * (size_t)e->rows * 2));
+    CK(e->vr.reserve(want));
     long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)(2 * want + 65536);
     if (mc > (1ll << 30)) mc = 1ll << 30;
     if (mc > e->max_cells) {
@@ -210,6 +213,7 @@ int run_sort(sphb_engine* e, bool carry_all) {
     e->cur = nxt;
     e->grid_valid = true;
     e->mask_valid = false;
+    e->vr_valid = false;
     e->bbox_valid = false; // k_key_hist re-armed the accumulator
     return SPHB_OK;
 }
@@ -218,15 +222,17 @@ int run_sort(sphb_engine* e, bool carry_all) {
 int run_density(sphb_engine* e, bool with_aux) {
     const int n = (int)e->n;
     auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
-    LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->aux[e->cur].p, e->mask.p, n);
+    LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->vel[e->cur].p, e->aux[e->cur].p,
+           e->vr.p, e->mask.p, n);
     CK(cudaGetLastError());
     e->mask_valid = true;
+    e->vr_valid = with_aux;
     return SPHB_OK;
 }
 
-template <bool kFused, bool kBBox, bool kAccel>
+template <bool kFused, bool kBBox, bool kAccel, bool kDerive>
 auto force_kernel(int rows) {
-    return rows == 9 ? k_force<kFused, kBBox, kAccel, 9> : k_force<kFused, kBBox, kAccel, 25>;
+    return rows == 9 ? k_force<kFused, kBBox, kAccel, 9, kDerive> : k_force<kFused, kBBox, kAccel, 25, kDerive>;
 }
 
 int check_ready(sphb_engine* e) {
@@ -303,7 +309,7 @@ void sphb_destroy(sphb_engine* e) {
     for (int b = 0; b < 2; b++) {
         e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
     }
-    e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release();
+    e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release(); e->vr.release();
     e->cell_start.release(); e->block_sums.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release();
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
@@ -357,6 +363,7 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
     e->have_state = true;
     e->grid_valid = false;
     e->mask_valid = false;
+    e->vr_valid = false;
     e->bbox_valid = false;
     e->aos_valid = true;
     return SPHB_OK;
@@ -384,6 +391,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
     e->have_state = true;
     e->grid_valid = false;
     e->mask_valid = false;
+    e->vr_valid = false;
     e->bbox_valid = false;
     e->aos_valid = false;
     return SPHB_OK;
@@ -436,9 +444,10 @@ int sphb_update_forces(sphb_engine* e) {
     if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
     if (!e->mask_valid && (rc = run_density(e, false))) return rc;
     const int n = (int)e->n, cur = e->cur;
-    auto kfn = force_kernel<false, false, true>(e->rows);
+    // vr_valid: rho/P in aux are this engine's own (update_density ran on this sorted state) -> two-gather kernel
+    auto kfn = e->vr_valid ? force_kernel<false, false, true, true>(e->rows) : force_kernel<false, false, true, false>(e->rows);
     LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p,
-           e->aux[cur].p, e->mask.p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
+           e->aux[cur].p, e->vr.p, e->mask.p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
     CK(cudaGetLastError());
     return SPHB_OK;
 }
@@ -452,6 +461,7 @@ int sphb_update_posvel(sphb_engine* e) {
     CK(cudaGetLastError());
     e->grid_valid = false;
     e->mask_valid = false;
+    e->vr_valid = false;
     e->bbox_valid = false;
     return SPHB_OK;
 }
@@ -465,6 +475,7 @@ int sphb_collision(sphb_engine* e) {
     CK(cudaGetLastError());
     e->grid_valid = false;
     e->mask_valid = false;
+    e->vr_valid = false;
     e->bbox_valid = false;
     return SPHB_OK;
 }
@@ -488,9 +499,9 @@ int sphb_step(sphb_engine* e, int nsteps) {
         if (timed) CK(cudaEventRecord(ev[2], e->stream));
         const int cur = e->cur, nxt = cur ^ 1;
         const int blocks = cdiv(n, 128);
-#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->mask.p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
-        auto kfn = bbox ? (acc ? force_kernel<true, true, true>(e->rows) : force_kernel<true, true, false>(e->rows))
-                        : (acc ? force_kernel<true, false, true>(e->rows) : force_kernel<true, false, false>(e->rows));
+#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->vr.p, e->mask.p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
+        auto kfn = bbox ? (acc ? force_kernel<true, true, true, true>(e->rows) : force_kernel<true, true, false, true>(e->rows))
+                        : (acc ? force_kernel<true, false, true, true>(e->rows) : force_kernel<true, false, false, true>(e->rows));
         LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS);
 #undef FORCE_ARGS
         CK(cudaGetLastError());
@@ -503,6 +514,7 @@ int sphb_step(sphb_engine* e, int nsteps) {
         e->cur = nxt;
         e->grid_valid = false;
         e->mask_valid = false;
+        e->vr_valid = false;
         e->bbox_valid = bbox;
         if (timed) {
             CK(cudaEventRecord(ev[3], e->stream));
@@ -743,6 +755,7 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     }
     e->grid_valid = false;
     e->mask_valid = false;
+    e->vr_valid = false;
     e->bbox_valid = false;
     e->aos_valid = false;
     if (counts) { counts[0] = (size_t)kept; counts[1] = (size_t)cl; counts[2] = (size_t)cr; counts[3] = (size_t)total; }
