@@ -195,6 +195,7 @@ def main():
     ap.add_argument("--no-accel", action="store_true", help="skip the per-particle acceleration output (72 B force kernel)")
     ap.add_argument("--domain", default="fixed", choices=["fixed", "bbox"])
     ap.add_argument("--cell-frac", type=float, default=1.0, help="grid cell edge as a fraction of the support radius h*h (>= 0.5)")
+    ap.add_argument("--cell-x-div", type=int, default=0, help="x pitch of the grid = cell / this (0 = engine default, 2)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -217,9 +218,12 @@ def main():
     ps, walls, (dlo, dhi) = make_workload(args.workload)
     n = len(ps)
     kw = dict(write_accel=0 if args.no_accel else 1)
-    if args.cell_frac != 1.0:
-        cell = float(np.float32(0.45) * np.float32(0.45)) * args.cell_frac
-        kw.update(cell_size=cell, max_cells=int(np.prod([(h - l) / cell + 2 for l, h in zip(dlo, dhi)])) + 4096)
+    xdiv = args.cell_x_div if args.cell_x_div > 0 else 2
+    cell = float(np.float32(0.45) * np.float32(0.45)) * args.cell_frac
+    if args.domain == "fixed":
+        ncell = ((dhi[0] - dlo[0]) / (cell / xdiv) + 2) * ((dhi[1] - dlo[1]) / cell + 2) * ((dhi[2] - dlo[2]) / cell + 2)
+        kw.update(max_cells=int(ncell) + 4096)
+    kw.update(cell_size=cell if args.cell_frac != 1.0 else 0.0, cell_x_div=args.cell_x_div)
     if args.domain == "fixed":
         kw.update(domain_mode=sph_b200.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi)
     eng = sph_b200.Engine(device=local, **kw)
@@ -294,7 +298,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload], "particles": n, "domain": args.domain, "cell_frac": args.cell_frac,
+        "config": {"workload": WORKLOADS[args.workload], "particles": n, "domain": args.domain, "cell_frac": args.cell_frac, "cell_x_div": xdiv,
                    "l2": "state (>= 32 B/particle x 2 buffers) exceeds the 126 MB L2" if n * 64 > 126e6 else
                          "state fits in L2: no flush between steps (steps are dependent, not repeats)",
                    "accel_output": not args.no_accel},

@@ -75,7 +75,11 @@ typedef struct sphb_params {
                               the reference has only planes */
     int64_t max_cells;     /* capacity of the cell table; 0 => chosen from the particle count at upload */
     int32_t write_accel;   /* 1 => sphb_step also stores per-particle acceleration (parity / viewers); 0 => skipped */
-    int32_t reserved[7];
+    int32_t cell_x_div;    /* the grid cell is cell_size / cell_x_div long in x (cell_size in y and z): the cells of a
+                              (y,z) row are contiguous in memory, so a finer x pitch only trims the candidate run
+                              from 3 cells to 2R + 2 cell_x.  0 => 2 (fastest measured on B200: finer pitches cost more in
+                              the sort and in L1 wavefronts than they save in tests).  1 => cubic cells */
+    int32_t reserved[6];
 } sphb_params;
 
 /* Fill *p with the reference's constants (main.cpp:30-41 and the literals of SphUtils.cpp). */
@@ -143,7 +147,7 @@ int sphb_host_unregister(void* ptr);
 int sphb_eval_kernels(sphb_engine* e, const float* xi, const float* xj, size_t count, float* w, float* grad, float* lap);
 
 /* Grid of the last sort, for the bit-exact grid test: cell_xyz[3n] in ORIGINAL particle order,
- * perm[n] = original index held by sorted slot s, dims[3], origin[3], cell size.  Any may be NULL. */
+ * perm[n] = original index held by sorted slot s, dims[3], origin[3], cell[3] (edge per axis).  Any may be NULL. */
 int sphb_get_cells(sphb_engine* e, int32_t* cell_xyz, int32_t* perm, int32_t* dims, float* origin, float* cell);
 
 /* Bounding box {minx,miny,minz,maxx,maxy,maxz} of the current positions (SphUtils.cpp:11-23). */

@@ -33,7 +33,7 @@ class Params(C.Structure):
 
 
 class Grid(C.Structure):
-    _fields_ = [("origin", C.c_float * 3), ("cell", C.c_float), ("dims", C.c_int * 3)]
+    _fields_ = [("origin", C.c_float * 3), ("cell", C.c_float * 3), ("dims", C.c_int * 3)]
 
 
 # main.cpp:30-41
@@ -131,14 +131,15 @@ class Oracle:
 
     def grid_from_bbox(self, bbox, cell, max_cells) -> Grid:
         g = Grid()
-        self.lib.orc_grid_from_bbox(_f3(bbox), C.c_float(cell), C.c_longlong(max_cells), C.byref(g))
+        cell = np.broadcast_to(np.asarray(cell, np.float32), (3,))
+        self.lib.orc_grid_from_bbox(_f3(bbox), _f3(cell), C.c_longlong(max_cells), C.byref(g))
         return g
 
     @staticmethod
     def make_grid(origin, cell, dims) -> Grid:
         g = Grid()
         g.origin[:] = [float(x) for x in origin]
-        g.cell = float(cell)
+        g.cell[:] = [float(x) for x in np.broadcast_to(np.asarray(cell, np.float32), (3,))]
         g.dims[:] = [int(x) for x in dims]
         return g
 

@@ -293,18 +293,18 @@ long orc_ref_update_cells(const orc_params* p, const orc_particle* ps, size_t n,
  * until it fits; clamping the coordinates keeps every pair within one cell of each other. */
 typedef struct {
     float origin[3];
-    float cell;
+    float cell[3]; /* edge per axis: the engine's cells are shorter in x (cell_x = cell / cell_x_div) */
     int dims[3];
 } orc_grid;
 
-void orc_grid_from_bbox(const float bbox[6], float cell, long long max_cells, orc_grid* g) {
+void orc_grid_from_bbox(const float bbox[6], const float cell[3], long long max_cells, orc_grid* g) {
     for (int a = 0; a < 3; a++) {
         g->origin[a] = bbox[a];
-        float ext = ceilf((bbox[3 + a] - bbox[a]) / cell);
+        g->cell[a] = cell[a];
+        float ext = ceilf((bbox[3 + a] - bbox[a]) / cell[a]);
         g->dims[a] = (ext < 1048575.0f) ? (int)ext + 1 : 1048576; /* cap also catches inf/NaN extents */
         if (g->dims[a] < 1) g->dims[a] = 1;
     }
-    g->cell = cell;
     while ((long long)g->dims[0] * g->dims[1] * g->dims[2] > max_cells) {
         int a = 0;
         if (g->dims[1] > g->dims[a]) a = 1;
@@ -324,7 +324,7 @@ void orc_bbox(const orc_particle* ps, size_t n, float bbox[6]) {
 }
 
 static inline int grid_coord(const orc_grid* g, float x, int a) {
-    float f = floorf((x - g->origin[a]) / g->cell);
+    float f = floorf((x - g->origin[a]) / g->cell[a]);
     /* clamp in float first so that far-away strays (or NaN) cannot overflow the int conversion */
     if (!(f >= 0.0f)) return 0;
     if (f >= (float)g->dims[a]) return g->dims[a] - 1;
@@ -371,7 +371,8 @@ static void cellctx_init(cellctx* c, const orc_params* p, const orc_particle* ps
     float bbox[6];
     orc_bbox(ps, n, bbox);
     /* a hair wider than the support so float rounding in the coordinate cannot hide a pair */
-    float cell = p->h * p->h * 1.001f;
+    float cell1 = p->h * p->h * 1.001f;
+    float cell[3] = {cell1, cell1, cell1};
     orc_grid_from_bbox(bbox, cell, (long long)4 * (long long)n + 4096, &c->g);
     long long ncell = (long long)c->g.dims[0] * c->g.dims[1] * c->g.dims[2];
     c->perm = (int*)malloc(sizeof(int) * (n ? n : 1));

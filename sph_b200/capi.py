@@ -50,7 +50,7 @@ class Params(C.Structure):
         ("wall_test_off", C.c_double), ("wall_test_lim", C.c_double),
         ("domain_mode", C.c_int32), ("domain_lo", C.c_float * 3), ("domain_hi", C.c_float * 3),
         ("periodic", C.c_int32 * 3), ("max_cells", C.c_int64), ("write_accel", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("cell_x_div", C.c_int32), ("reserved", C.c_int32 * 6),
     ]
 
 
@@ -276,9 +276,9 @@ class Engine:
         perm = np.zeros(n, np.int32)
         dims = np.zeros(3, np.int32)
         origin = np.zeros(3, np.float32)
-        cell = np.zeros(1, np.float32)
+        cell = np.zeros(3, np.float32)
         self._check(self.lib.sphb_get_cells(self.h, _ptr(xyz), _ptr(perm), _ptr(dims), _ptr(origin), _ptr(cell)))
-        return xyz, perm, dims, origin, float(cell[0])
+        return xyz, perm, dims, origin, cell
 
     def get_bbox(self) -> np.ndarray:
         b = np.zeros(6, np.float32)

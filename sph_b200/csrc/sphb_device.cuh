@@ -22,8 +22,8 @@ struct GridDesc {
     float cell[3]; // per axis (equal unless an axis is periodic and the cell was stretched to tile it)
     int dims[3];
     int ncell;     // dims[0]*dims[1]*dims[2]
-    int stencil;   // half width in cells: ceil(R / cell) (1 when cell >= R)
-    int pad;
+    int stencil;   // half width of the stencil in y and z cells: ceil(R / cell) (1 when cell >= R)
+    int stencil_x; // half width in x cells: ceil(R / cell_x)
 };
 
 // Bounding-box accumulator: floats mapped to order-preserving unsigned ints so atomicMin/Max work.
@@ -52,7 +52,9 @@ struct Consts {
     float dom_lo[3], dom_hi[3];
     int periodic[3];
     long long max_cells;
-    float cell;
+    float cell;   // cell edge in y and z
+    float cell_x; // cell edge in x (cell / cell_x_div)
+    int stencil_x;
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -183,8 +185,8 @@ __device__ __forceinline__ void derive_grid(const Consts& c, const BBoxAcc* acc,
 #pragma unroll
     for (int a = 0; a < 3; a++) {
         g.origin[a] = lo[a];
-        g.cell[a] = c.cell;
-        float ext = ceilf(__fdiv_rn(__fsub_rn(hi[a], lo[a]), c.cell));
+        g.cell[a] = a == 0 ? c.cell_x : c.cell;
+        float ext = ceilf(__fdiv_rn(__fsub_rn(hi[a], lo[a]), g.cell[a]));
         int d = (ext < 1048575.0f) ? (int)ext + 1 : 1048576; // also catches inf/NaN extents
         g.dims[a] = d < 1 ? 1 : d;
     }
@@ -197,7 +199,7 @@ __device__ __forceinline__ void derive_grid(const Consts& c, const BBoxAcc* acc,
     }
     g.ncell = g.dims[0] * g.dims[1] * g.dims[2];
     g.stencil = (c.cell >= c.h2) ? 1 : 2;
-    g.pad = 0;
+    g.stencil_x = c.stencil_x;
 }
 
 __global__ void __launch_bounds__(256) k_grid_setup(Consts c, const BBoxAcc* acc, GridDesc* out, int* __restrict__ cell_count) {
@@ -370,17 +372,19 @@ __device__ __forceinline__ float w_shape(const Consts& c, float d2) {
     return t * t * t;
 }
 
-// Candidate runs.  Around cell (cx,cy,cz) there are (2S+1)^2 rows (dz, dy); along x the 2S+1 cells of a
-// row are contiguous in the sorted arrays, so each row is ONE run [jb, je) of sorted slots.  Rows are
+// Candidate runs.  Around cell (cx,cy,cz) there are (2S+1)^2 rows (dz, dy); along x the 2Sx+1 cells of a
+// row are contiguous in the sorted arrays, so each row is ONE run [jb, je) of sorted slots.  Cells are
+// shorter in x than in y,z (cell_x = cell / cell_x_div): the run then spans 2R + 2 cell_x instead of 3R,
+// i.e. ~30 % fewer candidates to test for free (same number of runs, same two table look-ups per run).  Rows are
 // numbered canonically r = (dz+S)*(2S+1) + (dy+S) so that the density and force kernels agree on them;
 // a row outside the grid is the empty run.
 __device__ __forceinline__ void row_run(const GridDesc& g, const int* __restrict__ cell_start, int cx, int cy, int cz, int r,
                                         int& jb, int& je) {
-    const int S = g.stencil, W = 2 * S + 1;
+    const int S = g.stencil, W = 2 * S + 1, Sx = g.stencil_x;
     const int z = cz + r / W - S, y = cy + r % W - S;
     jb = je = 0;
     if (z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]) return;
-    const int x0 = max(cx - S, 0), x1 = min(cx + S, g.dims[0] - 1);
+    const int x0 = max(cx - Sx, 0), x1 = min(cx + Sx, g.dims[0] - 1);
     const int row = g.dims[0] * (y + g.dims[1] * z);
     jb = __ldg(cell_start + row + x0);
     je = __ldg(cell_start + row + x1 + 1);

@@ -141,6 +141,10 @@ void build_consts(sphb_engine* e) {
         c.periodic[a] = p.periodic[a];
     }
     c.cell = p.cell_size > 0.0f ? p.cell_size : c.h2;
+    const int div = p.cell_x_div > 0 ? p.cell_x_div : 2;
+    c.cell_x = c.cell / (float)div;
+    c.stencil_x = (int)ceilf(c.h2 / c.cell_x);
+    while ((float)c.stencil_x * c.cell_x < c.h2) c.stencil_x++; // float safety: the x stencil must cover R
 }
 
 int ensure_capacity(sphb_engine* e, size_t n) {
@@ -160,7 +164,8 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     e->rows = (e->c.cell >= e->c.h2) ? 9 : 25;
     CK(e->mask.reserve(want * (size_t)e->rows * 2));
     CK(e->vr.reserve(want));
-    long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)(2 * want + 65536);
+    const int div = e->params.cell_x_div > 0 ? e->params.cell_x_div : 2;
+    long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)div * (long long)(2 * want + 65536);
     if (mc > (1ll << 30)) mc = 1ll << 30;
     if (mc > e->max_cells) {
         CK(e->cell_start.reserve((size_t)mc + 2));
@@ -278,6 +283,7 @@ int sphb_create(const sphb_params* p, int device, sphb_engine** out) {
     if (p->cell_size != 0.0f && !(p->cell_size >= 0.5f * R)) return fail(SPHB_ERR_INVALID, "cell_size must be 0 or >= h*h/2");
     if (p->domain_mode != SPHB_DOMAIN_BBOX && p->domain_mode != SPHB_DOMAIN_FIXED) return fail(SPHB_ERR_INVALID, "bad domain_mode");
     if (p->periodic[0] || p->periodic[1] || p->periodic[2]) return fail(SPHB_ERR_INVALID, "periodic axes are not implemented yet");
+    if (p->cell_x_div < 0 || p->cell_x_div > 64) return fail(SPHB_ERR_INVALID, "cell_x_div must be in [0, 64]");
     if (p->domain_mode == SPHB_DOMAIN_FIXED)
         for (int a = 0; a < 3; a++)
             if (!(p->domain_hi[a] >= p->domain_lo[a])) return fail(SPHB_ERR_INVALID, "fixed domain needs hi >= lo");
@@ -592,7 +598,7 @@ int sphb_get_cells(sphb_engine* e, int32_t* cell_xyz, int32_t* perm, int32_t* di
     CK(cudaStreamSynchronize(e->stream));
     if (dims) { dims[0] = g.dims[0]; dims[1] = g.dims[1]; dims[2] = g.dims[2]; }
     if (origin) { origin[0] = g.origin[0]; origin[1] = g.origin[1]; origin[2] = g.origin[2]; }
-    if (cell) *cell = g.cell[0];
+    if (cell) { cell[0] = g.cell[0]; cell[1] = g.cell[1]; cell[2] = g.cell[2]; }
     return SPHB_OK;
 }
 

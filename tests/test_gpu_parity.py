@@ -107,7 +107,8 @@ def test_grid_default_scene_bbox_mode(eng, oracle):
     dims, origin, cell = check_grid(eng, oracle, ps)
     bbox = oracle.bbox(ps)
     assert np.array_equal(eng.get_bbox(), bbox)             # SphUtils.cpp:11-23
-    g = oracle.grid_from_bbox(bbox, cell, 2 * len(ps) + 65536)
+    g = oracle.grid_from_bbox(bbox, cell, 2 * (2 * len(ps) + 65536))      # default capacity: cell_x_div * (2n + 65536)
+    assert cell[0] == np.float32(cell[1] / np.float32(2)) and cell[1] == cell[2] == np.float32(0.45) * np.float32(0.45)
     assert list(g.dims) == list(dims) and list(g.origin) == list(origin)   # SphUtils.cpp:25-27 formula
 
 
@@ -132,7 +133,7 @@ def test_grid_fixed_domain_clamps(oracle):
     with sph_b200.Engine(domain_mode=sph_b200.DOMAIN_FIXED, domain_lo=(0, 0, 0), domain_hi=(4.3, 2.0, 1.8)) as e:
         dims, origin, cell = check_grid(e, oracle, ps)
         assert list(origin) == [0, 0, 0]
-        assert list(dims) == [int(np.ceil(np.float32(x) / np.float32(cell))) + 1 for x in (4.3, 2.0, 1.8)]
+        assert list(dims) == [int(np.ceil(np.float32(x) / np.float32(c))) + 1 for x, c in zip((4.3, 2.0, 1.8), cell)]
 
 
 def test_grid_capacity_halving(oracle):
@@ -244,12 +245,13 @@ def test_pair_force_antisymmetry(eng):
     assert np.all(np.abs(tot) <= 1e-5 * scale)
 
 
-@pytest.mark.parametrize("frac", [0.5, 0.75, 1.3])
-def test_other_cell_sizes(oracle, golden, frac):
-    """cell = frac * R: a 5x5x5 stencil below 1 (25 runs per particle), fewer, fatter cells above."""
+@pytest.mark.parametrize("frac,xdiv", [(0.5, 0), (0.75, 1), (1.3, 3), (1.0, 1), (1.0, 2), (1.0, 16)])
+def test_other_cell_sizes(oracle, golden, frac, xdiv):
+    """cell = frac * R: a 5x5 stencil of runs below 1 (25 runs per particle), fewer, fatter cells above;
+    cell_x_div: cubic cells (1) up to very thin x slices (16).  Same results, same bit-exact grid."""
     g = golden("block4096.npz")
     R = float(np.float32(0.45) * np.float32(0.45))
-    with sph_b200.Engine(cell_size=R * frac) as e:
+    with sph_b200.Engine(cell_size=R * frac, cell_x_div=xdiv) as e:
         ps = g["initial"].copy()
         e.upload(ps)
         e.update_density()
