@@ -408,71 +408,193 @@ __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
     return make_aux(rho, P);
 }
 
-// kAux: compute and store density/pressure.  kMask: store the neighbour masks.
+// One candidate run of ONE target, scalar: the general path (crowded runs, targets whose row differs from
+// their thread-mates', array tails).  Adds the run's W terms (self included) to `sum` and writes the two mask
+// words of row r.
+template <bool kAux, bool kMask>
+__device__ __forceinline__ void density_row_single(const Consts& c, const float4* __restrict__ posm, unsigned int* __restrict__ mask,
+                                                   int n, int i, const float4& pi, int r, int jb, int je, float& sum) {
+    const int jm = min(je, jb + kMaskBits);
+    unsigned int m0 = 0, m1 = 0; // bits enter at the top and slide down: after len steps bit k = candidate k
+    int j = jb;
+    const int jh = min(jm, jb + 32);
+    for (; j < jh; j++) {
+        const float4 pj = ldg4(posm + j);
+        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
+        if (kMask) m0 = (m0 >> 1) | ((d2 < c.R2) ? 0x80000000u : 0u);
+    }
+    if (kMask) m0 = (jh - jb) ? (m0 >> (32 - (jh - jb))) : 0u;
+    for (; j < jm; j++) {
+        const float4 pj = ldg4(posm + j);
+        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
+        if (kMask) m1 = (m1 >> 1) | ((d2 < c.R2) ? 0x80000000u : 0u);
+    }
+    if (kMask) m1 = (jm - jh) > 0 ? (m1 >> (32 - (jm - jh))) : 0u;
+    if (kAux)
+        for (; j < je; j++) { // beyond the mask: crowded run
+            const float4 pj = ldg4(posm + j);
+            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            sum = fmaf(pj.w, w_shape(c, fmaf(dx, dx, fmaf(dy, dy, dz * dz))), sum);
+        }
+    if (kMask) {
+        const int self = i - jb; // the self term is excluded by index (SphUtils.cpp:132,216)
+        if (self >= 0 && i < je) {
+            if (self < 32) m0 &= ~(1u << self);
+            else if (self < kMaskBits) m1 &= ~(1u << (self - 32));
+        }
+        mask[(size_t)(2 * r) * n + i] = m0;      // word w of row r covers candidates jb + 32*w ...
+        mask[(size_t)(2 * r + 1) * n + i] = m1;
+    }
+}
+
+// Density kernel proper.  Each thread owns kDT = 4 CONSECUTIVE sorted particles ("targets").  Neighbouring
+// slots are neighbouring particles, so the four share their candidate runs up to a cell or two in x: every
+// candidate is loaded once and tested against all four -- a quarter of the L1 wavefronts per test -- and the
+// four tests run as two packed-FP32 pairs (Blackwell FADD2 / FMUL2 / FFMA2: one issue slot, two lanes of
+// math), which is what this issue-bound loop needs (profiles/r1b: issue 83 %, L1 data pipe 75 %).
+//   u  = d2 - R^2            sign bit = "inside the support"  -> funnel-shifted straight into the mask word
+//   t  = -u / h^2 = h^2 - d2/h^2 ;  W ~ max(t, 0)^3
+// Union run of the four targets: [jb of the leftmost, je of the rightmost]; a candidate outside a target's own
+// run is at least R away from it in x, so its bit is (at most a rounding-level ~0 term) clear and the
+// per-target mask is the union mask shifted down by (own jb - union jb).
+constexpr int kDT = 4;
+
 template <bool kAux, bool kMask>
 __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                  const float4* __restrict__ posm, const float4* __restrict__ vel,
                                                  float4* __restrict__ aux, float4* __restrict__ vr,
                                                  unsigned int* __restrict__ mask, int n) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * kDT;
+    if (i0 >= n) return;
     const GridDesc g = *gd;
-    const float4 pi = ldg4(posm + i);
-    int cx, cy, cz;
-    cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
-    const int nrows = (2 * g.stencil + 1) * (2 * g.stencil + 1);
-    float sum = 0.0f;
-    for (int r = 0; r < nrows; r++) {
-        int jb, je;
-        row_run(g, cell_start, cx, cy, cz, r, jb, je);
-        const int jm = min(je, jb + kMaskBits);
-        unsigned int m0 = 0, m1 = 0; // bits enter at the top and slide down: after len steps bit k = candidate k
-        int j = jb;
-        const int jh = min(jm, jb + 32);
-#pragma unroll 4
-        for (; j < jh; j++) {
-            const float4 pj = ldg4(posm + j);
-            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-            if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
-            if (kMask) m0 = (m0 >> 1) | (!(d2 >= c.R2) ? 0x80000000u : 0u);
-        }
-        if (kMask) m0 = (jh - jb) ? (m0 >> (32 - (jh - jb))) : 0u;
-#pragma unroll 4
-        for (; j < jm; j++) {
-            const float4 pj = ldg4(posm + j);
-            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-            if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
-            if (kMask) m1 = (m1 >> 1) | (!(d2 >= c.R2) ? 0x80000000u : 0u);
-        }
-        if (kMask) m1 = (jm - jh) > 0 ? (m1 >> (32 - (jm - jh))) : 0u;
-        if (kAux)
-            for (; j < je; j++) { // beyond the mask: crowded run
-                const float4 pj = ldg4(posm + j);
-                const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                sum = fmaf(pj.w, w_shape(c, fmaf(dx, dx, fmaf(dy, dy, dz * dz))), sum);
+    const int nt = min(kDT, n - i0);
+    float4 pi[kDT];
+    int cx[kDT], cy[kDT], cz[kDT];
+#pragma unroll
+    for (int k = 0; k < kDT; k++) {
+        pi[k] = ldg4(posm + min(i0 + k, n - 1));
+        cell_key(g, pi[k].x, pi[k].y, pi[k].z, cx[k], cy[k], cz[k]);
+    }
+    const int S = g.stencil, Sx = g.stencil_x;
+    const int nrows = (2 * S + 1) * (2 * S + 1);
+    float sum[kDT] = {0.0f, 0.0f, 0.0f, 0.0f};
+    bool together = nt == kDT;
+#pragma unroll
+    for (int k = 1; k < kDT; k++) together &= (cy[k] == cy[0]) & (cz[k] == cz[0]);
+
+    if (!together) {
+#pragma unroll
+        for (int k = 0; k < kDT; k++)
+            if (k < nt)
+                for (int r = 0; r < nrows; r++) {
+                    int jb, je;
+                    row_run(g, cell_start, cx[k], cy[k], cz[k], r, jb, je);
+                    density_row_single<kAux, kMask>(c, posm, mask, n, i0 + k, pi[k], r, jb, je, sum[k]);
+                }
+    } else {
+        const int cxlo = min(min(cx[0], cx[1]), min(cx[2], cx[3])), cxhi = max(max(cx[0], cx[1]), max(cx[2], cx[3]));
+        const float2 nx01 = make_float2(-pi[0].x, -pi[1].x), ny01 = make_float2(-pi[0].y, -pi[1].y), nz01 = make_float2(-pi[0].z, -pi[1].z);
+        const float2 nx23 = make_float2(-pi[2].x, -pi[3].x), ny23 = make_float2(-pi[2].y, -pi[3].y), nz23 = make_float2(-pi[2].z, -pi[3].z);
+        const float2 nR2 = make_float2(-c.R2, -c.R2), nih2 = make_float2(-c.inv_h2, -c.inv_h2);
+        float2 acc01 = make_float2(0.0f, 0.0f), acc23 = make_float2(0.0f, 0.0f);
+        const int W = 2 * S + 1;
+        for (int r = 0; r < nrows; r++) {
+            const int z = cz[0] + r / W - S, y = cy[0] + r % W - S;
+            int jbu = 0, jeu = 0, jbk[kDT] = {0, 0, 0, 0};
+            const bool inside = !(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]);
+            if (inside) {
+                const int row = g.dims[0] * (y + g.dims[1] * z);
+                jbu = __ldg(cell_start + row + max(cxlo - Sx, 0));
+                jeu = __ldg(cell_start + row + min(cxhi + Sx, g.dims[0] - 1) + 1);
+#pragma unroll
+                for (int k = 0; k < kDT; k++) jbk[k] = (cx[k] == cxlo) ? jbu : __ldg(cell_start + row + max(cx[k] - Sx, 0));
             }
-        if (kMask) {
-            const int self = i - jb; // the self term is excluded by index (SphUtils.cpp:132,216)
-            if (self >= 0 && i < je) {
-                if (self < 32) m0 &= ~(1u << self);
-                else if (self < kMaskBits) m1 &= ~(1u << (self - 32));
+            if (jeu - jbu > kMaskBits) { // crowded union: per-target general path for this row
+#pragma unroll
+                for (int k = 0; k < kDT; k++) {
+                    int jb, je;
+                    row_run(g, cell_start, cx[k], cy[k], cz[k], r, jb, je);
+                    density_row_single<kAux, kMask>(c, posm, mask, n, i0 + k, pi[k], r, jb, je, sum[k]);
+                }
+                continue;
             }
-            mask[(size_t)(2 * r) * n + i] = m0;      // word w of row r covers candidates jb + 32*w ...
-            mask[(size_t)(2 * r + 1) * n + i] = m1;
+            unsigned int mw[2][kDT];
+#pragma unroll
+            for (int w = 0; w < 2; w++) {
+                const int ja = min(jeu, jbu + 32 * w), jz = min(jeu, jbu + 32 * (w + 1));
+                unsigned int m[kDT] = {0u, 0u, 0u, 0u};
+#pragma unroll 2
+                for (int j = ja; j < jz; j++) {
+                    const float4 pj = ldg4(posm + j);
+                    const float2 xx = make_float2(pj.x, pj.x), yy = make_float2(pj.y, pj.y), zz = make_float2(pj.z, pj.z), mm = make_float2(pj.w, pj.w);
+                    {
+                        const float2 dx = __fadd2_rn(xx, nx01), dy = __fadd2_rn(yy, ny01), dz = __fadd2_rn(zz, nz01);
+                        const float2 d2 = __ffma2_rn(dx, dx, __ffma2_rn(dy, dy, __fmul2_rn(dz, dz)));
+                        const float2 u = __fadd2_rn(d2, nR2);
+                        if (kMask) {
+                            m[0] = __funnelshift_l(__float_as_uint(u.x), m[0], 1);
+                            m[1] = __funnelshift_l(__float_as_uint(u.y), m[1], 1);
+                        }
+                        if (kAux) {
+                            float2 t = __fmul2_rn(u, nih2);
+                            t.x = fmaxf(t.x, 0.0f);
+                            t.y = fmaxf(t.y, 0.0f);
+                            acc01 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc01);
+                        }
+                    }
+                    {
+                        const float2 dx = __fadd2_rn(xx, nx23), dy = __fadd2_rn(yy, ny23), dz = __fadd2_rn(zz, nz23);
+                        const float2 d2 = __ffma2_rn(dx, dx, __ffma2_rn(dy, dy, __fmul2_rn(dz, dz)));
+                        const float2 u = __fadd2_rn(d2, nR2);
+                        if (kMask) {
+                            m[2] = __funnelshift_l(__float_as_uint(u.x), m[2], 1);
+                            m[3] = __funnelshift_l(__float_as_uint(u.y), m[3], 1);
+                        }
+                        if (kAux) {
+                            float2 t = __fmul2_rn(u, nih2);
+                            t.x = fmaxf(t.x, 0.0f);
+                            t.y = fmaxf(t.y, 0.0f);
+                            acc23 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc23);
+                        }
+                    }
+                }
+                // the bits went in newest-lowest: candidate q of this word sits at bit (len-1-q); put it at bit q
+                const int len = jz - ja;
+#pragma unroll
+                for (int k = 0; k < kDT; k++) mw[w][k] = len ? (__brev(m[k]) >> (32 - len)) : 0u;
+            }
+            if (kMask) {
+#pragma unroll
+                for (int k = 0; k < kDT; k++) {
+                    unsigned long long m64 = ((unsigned long long)mw[1][k] << 32) | mw[0][k];
+                    m64 >>= (jbk[k] - jbu); // union-relative -> relative to this target's own run
+                    const int self = i0 + k - jbk[k];
+                    if (r == (nrows >> 1) && self >= 0 && self < kMaskBits) m64 &= ~(1ull << self); // self excluded by index
+                    mask[(size_t)(2 * r) * n + i0 + k] = (unsigned int)m64;
+                    mask[(size_t)(2 * r + 1) * n + i0 + k] = (unsigned int)(m64 >> 32);
+                }
+            }
         }
+        sum[0] += acc01.x; sum[1] += acc01.y; sum[2] += acc23.x; sum[3] += acc23.y;
     }
     if (kAux) {
-        // self term: every run above included j == i exactly once (its own cell's row); take it out again
-        sum -= pi.w * (c.h2 * c.h2 * c.h2);
-        const float4 a = finish_density(c, sum);
-        aux[i] = a;
-        // the force kernel gathers two records per neighbour: posm and (vx, vy, vz, rho); P, sqrt|P/rho| and
-        // 1/rho are functions of rho and are recomputed there (two gathers instead of three: the kernel is
-        // bound by L1 gather wavefronts, profiles/r1b)
-        const float4 v = ldg4(vel + i);
-        vr[i] = make_float4(v.x, v.y, v.z, a.x);
+#pragma unroll
+        for (int k = 0; k < kDT; k++) {
+            if (k >= nt) break;
+            // self term: the runs above included j == i exactly once (its own cell's row); take it out again
+            const float s = sum[k] - pi[k].w * (c.h2 * c.h2 * c.h2);
+            const float4 a = finish_density(c, s);
+            aux[i0 + k] = a;
+            // the force kernel gathers two records per neighbour: posm and (vx, vy, vz, rho); P, sqrt|P/rho| and
+            // 1/rho are functions of rho and are recomputed there (two gathers instead of three: the kernel is
+            // bound by L1 gather wavefronts, profiles/r1b)
+            const float4 v = ldg4(vel + i0 + k);
+            vr[i0 + k] = make_float4(v.x, v.y, v.z, a.x);
+        }
     }
 }
 

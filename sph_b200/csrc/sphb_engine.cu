@@ -227,8 +227,8 @@ int run_sort(sphb_engine* e, bool carry_all) {
 int run_density(sphb_engine* e, bool with_aux) {
     const int n = (int)e->n;
     auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
-    LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->vel[e->cur].p, e->aux[e->cur].p,
-           e->vr.p, e->mask.p, n);
+    LAUNCH(e, kfn, cdiv(cdiv(n, kDT), 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->vel[e->cur].p,
+           e->aux[e->cur].p, e->vr.p, e->mask.p, n);
     CK(cudaGetLastError());
     e->mask_valid = true;
     e->vr_valid = with_aux;
