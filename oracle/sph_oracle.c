@@ -312,6 +312,10 @@ void orc_grid_from_bbox(const float bbox[6], const float cell[3], long long max_
         if (g->dims[a] == 1) break;
         g->dims[a] = (g->dims[a] + 1) / 2;
     }
+    while ((long long)g->dims[1] * g->dims[2] > (1 << 22)) { /* same policy for the number of (y,z) rows */
+        int a = g->dims[2] > g->dims[1] ? 2 : 1;
+        g->dims[a] = (g->dims[a] + 1) / 2;
+    }
 }
 
 void orc_bbox(const orc_particle* ps, size_t n, float bbox[6]) {

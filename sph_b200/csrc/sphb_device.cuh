@@ -15,6 +15,7 @@
 namespace sphb {
 
 constexpr int kMaxWalls = 16;
+constexpr int kMaxRows = 1 << 22; // cap on dims[1]*dims[2] ((y,z) rows of cells): bounds the row-group table
 
 // Device-resident description of the uniform grid (rebuilt every step by k_grid_setup).
 struct GridDesc {
@@ -195,6 +196,10 @@ __device__ __forceinline__ void derive_grid(const Consts& c, const BBoxAcc* acc,
         if (g.dims[1] > g.dims[a]) a = 1;
         if (g.dims[2] > g.dims[a]) a = 2;
         if (g.dims[a] == 1) break;
+        g.dims[a] = (g.dims[a] + 1) / 2;
+    }
+    while ((long long)g.dims[1] * g.dims[2] > kMaxRows) { // same policy for the number of (y,z) rows
+        const int a = g.dims[2] > g.dims[1] ? 2 : 1;
         g.dims[a] = (g.dims[a] + 1) / 2;
     }
     g.ncell = g.dims[0] * g.dims[1] * g.dims[2];
@@ -408,6 +413,53 @@ __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
     return make_aux(rho, P);
 }
 
+// Row groups.  The density kernel gives each thread kDT consecutive sorted particles of ONE (y,z) row of cells,
+// so that they always share their candidate runs.  Row rho holds the slots [cell_start[rho*nx],
+// cell_start[(rho+1)*nx]) and is cut into ceil(len / kDT) groups; gstart = exclusive scan of the group counts
+// (nrows + 1 entries), one block.  Thread t of the density kernel finds its row by binary search in gstart.
+constexpr int kDT = 4;
+constexpr int kRgThreads = 1024;
+
+__global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                          int* __restrict__ gstart) {
+    __shared__ int s_warp[kRgThreads / 32];
+    __shared__ int s_carry;
+    const int nx = gd->dims[0], nrows = gd->dims[1] * gd->dims[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nrows; base += kRgThreads) {
+        const int rho = base + threadIdx.x;
+        int v = 0;
+        if (rho < nrows) v = (cell_start[(rho + 1) * nx] - cell_start[rho * nx] + kDT - 1) / kDT;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const int carry = s_carry;
+        const int ex = carry + (warp ? s_warp[warp - 1] : 0) + inc - v;
+        if (rho < nrows) gstart[rho] = ex;
+        __syncthreads();
+        if (threadIdx.x == kRgThreads - 1) s_carry = ex + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) gstart[nrows] = s_carry;
+}
+
 // One candidate run of ONE target, scalar: the general path (crowded runs, targets whose row differs from
 // their thread-mates', array tails).  Adds the run's W terms (self included) to `sum` and writes the two mask
 // words of row r.
@@ -461,41 +513,36 @@ __device__ __forceinline__ void density_row_single(const Consts& c, const float4
 // Union run of the four targets: [jb of the leftmost, je of the rightmost]; a candidate outside a target's own
 // run is at least R away from it in x, so its bit is (at most a rounding-level ~0 term) clear and the
 // per-target mask is the union mask shifted down by (own jb - union jb).
-constexpr int kDT = 4;
-
 template <bool kAux, bool kMask>
 __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                 const int* __restrict__ gstart,
                                                  const float4* __restrict__ posm, const float4* __restrict__ vel,
                                                  float4* __restrict__ aux, float4* __restrict__ vr,
                                                  unsigned int* __restrict__ mask, int n) {
-    const int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * kDT;
-    if (i0 >= n) return;
     const GridDesc g = *gd;
-    const int nt = min(kDT, n - i0);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nrows_grid = g.dims[1] * g.dims[2];
+    if (t >= __ldg(gstart + nrows_grid)) return;
+    // binary search: the row rho with gstart[rho] <= t < gstart[rho + 1]
+    int lo_r = 0, hi_r = nrows_grid;
+    while (hi_r - lo_r > 1) {
+        const int mid = (lo_r + hi_r) >> 1;
+        if (__ldg(gstart + mid) <= t) lo_r = mid; else hi_r = mid;
+    }
+    const int row_end = __ldg(cell_start + (lo_r + 1) * g.dims[0]);
+    const int i0 = __ldg(cell_start + lo_r * g.dims[0]) + (t - __ldg(gstart + lo_r)) * kDT;
+    const int nt = min(kDT, row_end - i0); // the tail group of a row is short: extra targets repeat the last one
     float4 pi[kDT];
     int cx[kDT], cy[kDT], cz[kDT];
 #pragma unroll
     for (int k = 0; k < kDT; k++) {
-        pi[k] = ldg4(posm + min(i0 + k, n - 1));
+        pi[k] = ldg4(posm + i0 + min(k, nt - 1));
         cell_key(g, pi[k].x, pi[k].y, pi[k].z, cx[k], cy[k], cz[k]);
     }
     const int S = g.stencil, Sx = g.stencil_x;
     const int nrows = (2 * S + 1) * (2 * S + 1);
     float sum[kDT] = {0.0f, 0.0f, 0.0f, 0.0f};
-    bool together = nt == kDT;
-#pragma unroll
-    for (int k = 1; k < kDT; k++) together &= (cy[k] == cy[0]) & (cz[k] == cz[0]);
-
-    if (!together) {
-#pragma unroll
-        for (int k = 0; k < kDT; k++)
-            if (k < nt)
-                for (int r = 0; r < nrows; r++) {
-                    int jb, je;
-                    row_run(g, cell_start, cx[k], cy[k], cz[k], r, jb, je);
-                    density_row_single<kAux, kMask>(c, posm, mask, n, i0 + k, pi[k], r, jb, je, sum[k]);
-                }
-    } else {
+    {
         const int cxlo = min(min(cx[0], cx[1]), min(cx[2], cx[3])), cxhi = max(max(cx[0], cx[1]), max(cx[2], cx[3]));
         const float2 nx01 = make_float2(-pi[0].x, -pi[1].x), ny01 = make_float2(-pi[0].y, -pi[1].y), nz01 = make_float2(-pi[0].z, -pi[1].z);
         const float2 nx23 = make_float2(-pi[2].x, -pi[3].x), ny23 = make_float2(-pi[2].y, -pi[3].y), nz23 = make_float2(-pi[2].z, -pi[3].z);
@@ -516,6 +563,7 @@ __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __res
             if (jeu - jbu > kMaskBits) { // crowded union: per-target general path for this row
 #pragma unroll
                 for (int k = 0; k < kDT; k++) {
+                    if (k >= nt) break;
                     int jb, je;
                     row_run(g, cell_start, cx[k], cy[k], cz[k], r, jb, je);
                     density_row_single<kAux, kMask>(c, posm, mask, n, i0 + k, pi[k], r, jb, je, sum[k]);
@@ -574,8 +622,10 @@ __global__ void __launch_bounds__(128) k_density(Consts c, const GridDesc* __res
                     m64 >>= (jbk[k] - jbu); // union-relative -> relative to this target's own run
                     const int self = i0 + k - jbk[k];
                     if (r == (nrows >> 1) && self >= 0 && self < kMaskBits) m64 &= ~(1ull << self); // self excluded by index
-                    mask[(size_t)(2 * r) * n + i0 + k] = (unsigned int)m64;
-                    mask[(size_t)(2 * r + 1) * n + i0 + k] = (unsigned int)(m64 >> 32);
+                    if (k < nt) {
+                        mask[(size_t)(2 * r) * n + i0 + k] = (unsigned int)m64;
+                        mask[(size_t)(2 * r + 1) * n + i0 + k] = (unsigned int)(m64 >> 32);
+                    }
                 }
             }
         }

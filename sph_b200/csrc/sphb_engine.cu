@@ -73,6 +73,7 @@ struct sphb_engine {
     int rows = 9;                    // (2*stencil+1)^2
     DevBuf<int> cell_start; // max_cells + 1 (+ slack)
     DevBuf<int> block_sums;
+    DevBuf<int> row_groups; // exclusive scan of ceil(row length / kDT) over the (y,z) rows of cells (kMaxRows + 2)
     DevBuf<float> aos;      // staging for host AoS records
     DevBuf<float> scratch;  // eval_kernels, cells download
     DevBuf<int> mg_counts;  // multi-GPU pack: 3 per block, then totals[3] and recv_counts[4]
@@ -170,6 +171,7 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     if (mc > e->max_cells) {
         CK(e->cell_start.reserve((size_t)mc + 2));
         CK(e->block_sums.reserve((size_t)cdiv(mc + 2, kScanTile) + 1));
+        CK(e->row_groups.reserve((size_t)(mc + 2 < kMaxRows + 2 ? mc + 2 : kMaxRows + 2)));
         e->max_cells = mc;
     }
     e->c.max_cells = e->max_cells;
@@ -207,6 +209,7 @@ int run_sort(sphb_engine* e, bool carry_all) {
     LAUNCH(e, k_scan_reduce, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
     LAUNCH(e, k_scan_top, 1, kScanThreads, 0, e->d_grid, e->block_sums.p);
     LAUNCH(e, k_scan_apply, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
+    LAUNCH(e, k_row_groups, 1, kRgThreads, 0, e->d_grid, e->cell_start.p, e->row_groups.p);
     LAUNCH(e, k_scatter, pb, 256, 0, e->key.p, e->slot.p, e->oid[cur].p, e->cell_start.p, e->pairs.p, n);
     if (carry_all)
         LAUNCH(e, k_rank_gather<true>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
@@ -227,8 +230,11 @@ int run_sort(sphb_engine* e, bool carry_all) {
 int run_density(sphb_engine* e, bool with_aux) {
     const int n = (int)e->n;
     auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
-    LAUNCH(e, kfn, cdiv(cdiv(n, kDT), 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->vel[e->cur].p,
-           e->aux[e->cur].p, e->vr.p, e->mask.p, n);
+    // groups <= n/kDT + (number of non-empty rows); threads beyond the device-side total exit at once
+    long long rows_bound = e->max_cells < kMaxRows ? e->max_cells : kMaxRows;
+    if (rows_bound > n) rows_bound = n;
+    LAUNCH(e, kfn, cdiv(cdiv(n, kDT) + rows_bound, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+           e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, n);
     CK(cudaGetLastError());
     e->mask_valid = true;
     e->vr_valid = with_aux;
@@ -316,7 +322,7 @@ void sphb_destroy(sphb_engine* e) {
         e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
     }
     e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release(); e->vr.release();
-    e->cell_start.release(); e->block_sums.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release();
+    e->cell_start.release(); e->block_sums.release(); e->row_groups.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release();
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
     if (e->ev) {
