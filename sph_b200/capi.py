@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsphb200.so")
+LIB_PATH = os.environ.get("SPHB_LIB") or os.path.join(_HERE, "libsphb200.so")   # SPHB_LIB: an experimental build of the same library
 
 # Host exchange records, byte-compatible with the reference:
 # SPH/Particle.hpp:42-50 (52 B), SPH/Wall.hpp:28-31 (32 B), SPH/Sphere.hpp:29-33 (44 B)
