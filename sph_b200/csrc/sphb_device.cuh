@@ -460,6 +460,38 @@ __global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __res
     if (threadIdx.x == 0) gstart[nrows] = s_carry;
 }
 
+// The row rho with gstart[rho] <= t < gstart[rho + 1] (t = density-group index).  One 32-ary search per WARP
+// for its first thread (three dependent loads for 32 K rows instead of fifteen), then each lane walks on from
+// there: a warp covers ~128 particles, i.e. almost always one or two rows.  All 32 lanes must call it.
+__device__ __forceinline__ int find_row(const int* __restrict__ gstart, int nrows_grid, int t) {
+    const int lane = threadIdx.x & 31;
+    const int t0 = __shfl_sync(0xffffffffu, t, 0);
+    int lo = 0, hi = nrows_grid; // invariant: gstart[lo] <= t0 < gstart[hi]
+    while (hi - lo > 1) {
+        const int step = (hi - lo + 31) >> 5;
+        const int probe = min(lo + (lane + 1) * step, hi);
+        const bool le = probe < hi ? (__ldg(gstart + probe) <= t0) : false;
+        const int cnt = __popc(__ballot_sync(0xffffffffu, le)); // probes are ascending: the first cnt satisfy <=
+        const int nlo = lo + cnt * step, nhi = min(lo + (cnt + 1) * step, hi);
+        lo = cnt ? min(nlo, hi - 1) : lo;
+        hi = nhi;
+        if (lo >= hi) hi = lo + 1;
+    }
+    int lo_r = lo;
+    // lanes further right: walk forward (bounded), then finish with a plain binary search if rows are sparse
+    int steps = 0;
+    while (lo_r + 1 < nrows_grid && __ldg(gstart + lo_r + 1) <= t && steps < 8) { ++lo_r; ++steps; }
+    if (lo_r + 1 < nrows_grid && __ldg(gstart + lo_r + 1) <= t) {
+        int a = lo_r, b = nrows_grid;
+        while (b - a > 1) {
+            const int mid = (a + b) >> 1;
+            if (__ldg(gstart + mid) <= t) a = mid; else b = mid;
+        }
+        lo_r = a;
+    }
+    return lo_r;
+}
+
 // One candidate run of ONE target, scalar: the general path (crowded runs, targets whose row differs from
 // their thread-mates', array tails).  Adds the run's W terms (self included) to `sum` and writes the two mask
 // words of row r.
@@ -532,37 +564,7 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
     if ((t_raw & ~31) >= ngroups) return;          // whole warp beyond the last group
     const bool live = t_raw < ngroups;
     const int t = live ? t_raw : ngroups - 1;       // spare lanes of the last warp shadow the last group (warp-wide votes below)
-    // The row rho with gstart[rho] <= t < gstart[rho + 1].  One 32-ary search per WARP for its first thread
-    // (three dependent loads for 32 K rows instead of fifteen), then each lane walks on from there: a warp
-    // covers 128 particles, i.e. almost always one or two rows.
-    int lo_r;
-    {
-        const int lane = threadIdx.x & 31;
-        const int t0 = __shfl_sync(0xffffffffu, t, 0);
-        int lo = 0, hi = nrows_grid; // invariant: gstart[lo] <= t0 < gstart[hi]
-        while (hi - lo > 1) {
-            const int step = (hi - lo + 31) >> 5;
-            const int probe = min(lo + (lane + 1) * step, hi);
-            const bool le = probe < hi ? (__ldg(gstart + probe) <= t0) : false;
-            const int cnt = __popc(__ballot_sync(0xffffffffu, le)); // probes are ascending: the first cnt satisfy <=
-            const int nlo = lo + cnt * step, nhi = min(lo + (cnt + 1) * step, hi);
-            lo = cnt ? min(nlo, hi - 1) : lo;
-            hi = nhi;
-            if (lo >= hi) hi = lo + 1;
-        }
-        lo_r = lo;
-        // lanes further right: walk forward (bounded), then finish with a plain binary search if rows are sparse
-        int steps = 0;
-        while (lo_r + 1 < nrows_grid && __ldg(gstart + lo_r + 1) <= t && steps < 8) { ++lo_r; ++steps; }
-        if (lo_r + 1 < nrows_grid && __ldg(gstart + lo_r + 1) <= t) {
-            int a = lo_r, b = nrows_grid;
-            while (b - a > 1) {
-                const int mid = (a + b) >> 1;
-                if (__ldg(gstart + mid) <= t) a = mid; else b = mid;
-            }
-            lo_r = a;
-        }
-    }
+    const int lo_r = find_row(gstart, nrows_grid, t);
     if (!live) return;
     const int row_end = __ldg(cell_start + (lo_r + 1) * g.dims[0]);
     const int i0 = __ldg(cell_start + lo_r * g.dims[0]) + (t - __ldg(gstart + lo_r)) * kDT;
