@@ -155,6 +155,10 @@ int sphb_get_bbox(sphb_engine* e, float bbox[6]);
 
 size_t sphb_count(const sphb_engine* e);
 
+/* Number of particles whose position or velocity is NaN or infinite (the reference propagates NaN silently once
+ * two particles coincide, SphUtils.cpp:75; this lets a driver notice).  Synchronises. */
+int sphb_count_nonfinite(sphb_engine* e, size_t* count);
+
 /* Per-phase GPU time, measured with CUDA events on the engine's stream around the kernels of each
  * sphb_step step (no host synchronisation is added).  sphb_enable_timing(e, 1) starts (and resets) the
  * record, up to 256 steps; sphb_get_timing synchronises and returns the AVERAGE ms per step over the

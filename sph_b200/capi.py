@@ -61,7 +61,7 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
+    "sphb_count_nonfinite", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
 ]
 
 _lib = None
@@ -104,6 +104,7 @@ def load_library() -> C.CDLL:
     L.sphb_get_bbox.argtypes = [vp, vp]
     L.sphb_count.argtypes = [vp]
     L.sphb_count.restype = sz
+    L.sphb_count_nonfinite.argtypes = [vp, C.POINTER(sz)]
     L.sphb_enable_timing.argtypes = [vp, i32]
     L.sphb_get_timing.argtypes = [vp, vp, vp]
     L.sphb_launch_count.argtypes = [vp]
@@ -287,6 +288,11 @@ class Engine:
 
     def count(self) -> int:
         return int(self.lib.sphb_count(self.h))
+
+    def count_nonfinite(self) -> int:
+        k = C.c_size_t(0)
+        self._check(self.lib.sphb_count_nonfinite(self.h, C.byref(k)))
+        return int(k.value)
 
     def enable_timing(self, on: bool = True):
         self._check(self.lib.sphb_enable_timing(self.h, int(on)))

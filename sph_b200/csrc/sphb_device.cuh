@@ -958,6 +958,21 @@ __global__ void __launch_bounds__(256) k_cells_xyz(const GridDesc* __restrict__ 
     xyz[3 * o] = cx; xyz[3 * o + 1] = cy; xyz[3 * o + 2] = cz;
 }
 
+// NaN / inf census (debug aid: the reference spreads NaN silently once two particles coincide)
+__global__ void __launch_bounds__(256) k_count_nonfinite(const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
+                                                         unsigned long long* __restrict__ out) {
+    int bad = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 p = posm[i], v = vel[i];
+        const float s = p.x + p.y + p.z + v.x + v.y + v.z; // NaN or inf anywhere makes s non-finite (inf - inf gives NaN)
+        bad += !(fabsf(s) <= 3.0e38f) || !(fabsf(p.x) <= 3.0e38f) || !(fabsf(v.x) <= 3.0e38f);
+    }
+    const int c = __syncthreads_count(0) + 0; // keep the block converged
+    (void)c;
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out, (unsigned long long)bad);
+}
+
 // device-to-device upload helper: ids default to 0..n-1
 __global__ void __launch_bounds__(256) k_fill_iota(int* __restrict__ ids, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

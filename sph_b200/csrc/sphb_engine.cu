@@ -629,6 +629,26 @@ int sphb_get_bbox(sphb_engine* e, float bbox[6]) {
 
 size_t sphb_count(const sphb_engine* e) { return e ? e->n : 0; }
 
+int sphb_count_nonfinite(sphb_engine* e, size_t* count) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (!count) return fail(SPHB_ERR_INVALID, "null count");
+    *count = 0;
+    if (e->n == 0) return SPHB_OK;
+    CK(e->scratch.reserve(4));
+    unsigned long long* d = (unsigned long long*)e->scratch.p;
+    CK(cudaMemsetAsync(d, 0, sizeof(unsigned long long), e->stream));
+    int blocks = cdiv(e->n, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    LAUNCH(e, k_count_nonfinite, blocks, 256, 0, e->posm[e->cur].p, e->vel[e->cur].p, (int)e->n, d);
+    CK(cudaGetLastError());
+    unsigned long long h = 0;
+    CK(cudaMemcpyAsync(&h, d, sizeof h, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    *count = (size_t)h;
+    return SPHB_OK;
+}
+
 int sphb_enable_timing(sphb_engine* e, int on) {
     if (!e) return fail(SPHB_ERR_INVALID, "null engine");
     int rc = use_device(e);

@@ -178,8 +178,18 @@ def bench_main(args, world, rank, local):
     del ps
     eng.upload(host_np)
 
+    eng.update_cells()
+    init = [torch.from_numpy(a).cuda() for a in eng.download_soa()[:2]]   # this rank's initial owned state, on the device
+    init[1][:, 3] = 1.0
+    since_reset = [0]
+
     def one_step():
+        # the reference's scheme blows up on deep pools after ~35 steps (bench.py --reset-every): start over in time
+        if args.reset_every > 0 and since_reset[0] >= args.reset_every:
+            eng.upload_soa_device(init[0].data_ptr(), init[1].data_ptr(), n_own)
+            since_reset[0] = 0
         sr.step(dist, left, right)
+        since_reset[0] += 1
 
     for _ in range(max(3, args.warmup)):
         one_step()
@@ -204,6 +214,8 @@ def bench_main(args, world, rank, local):
     launches = eng.launch_count() - launches0
     phase, timed = eng.get_timing()
     eng.enable_timing(False)
+    bad = eng.count_nonfinite()
+    assert bad == 0, f"rank {rank}: {bad} non-finite particles after the timed steps"
     _, vel = sr.owned()
     owned = torch.tensor([len(vel)], device="cuda", dtype=torch.int64)
     dist.all_reduce(owned)

@@ -179,3 +179,11 @@ def block_drop_section(rank, world, scale=1, seed=1234):
     blk_pos, blk_vel = lattice_block(bx, by, bz, s, (off + x0, top, off), seed=seed, jitter=0.2, index0=per * rank + px * py * pz)
     blk_vel[:, 1] = -1.0
     return make_particles(np.concatenate([pool_pos, blk_pos]), np.concatenate([pool_vel, blk_vel]))
+
+
+def shallow_pool(nx=96, nz=96, layers=3, seed=1234, jitter=0.2):
+    """The reference's own kind of scene (main.cpp:490-505: a 3-layer sheet of particles 0.1 above the floor of a
+    box), at any width: the only kind its scheme (dt = 0.033, k = 100, CFL ~ 3.7) sustains for hundreds of steps.
+    Used for the long-run conservation checks."""
+    pos, vel = lattice_block(nx, layers, nz, 0.1, (0.1, 0.1, 0.1), seed=seed, jitter=jitter)
+    return make_particles(pos, vel), tank_walls(nx * 0.1 + 0.2, nz * 0.1 + 0.2)
