@@ -129,20 +129,21 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_baseline_port(sample_side=64):
+def cpu_baseline_port(sample_side=144, steps=8):
     """The oracle's cell-list restatement (bit-identical to the reference's loops) on all host cores, on a bounded
-    sample of the same kind of fluid: a jittered sample_side^3 block at the bench's spacing, one step."""
+    sample of the same kind of fluid: a jittered sample_side^3 block at the bench's spacing, `steps` steps
+    (sized for roughly 10 s of CPU work)."""
     from oracle.oracle import Oracle
     from sph_b200 import scenes
     orc = Oracle()
     ps, walls = scenes.dam_break(sample_side, sample_side, sample_side)
     threads = orc.max_threads()
     t0 = time.perf_counter()
-    orc.step(ps, walls, 1, cells=True, threads=threads)
+    orc.step(ps, walls, steps, cells=True, threads=threads)
     dt = time.perf_counter() - t0
-    return {"value": len(ps) / dt, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"1 step of a jittered {sample_side}^3 = {len(ps)} particle block (same spacing/jitter as the workload), "
-                      f"oracle cell-list restatement with OpenMP, {dt:.2f} s"}
+    return {"value": len(ps) * steps / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{steps} steps of a jittered {sample_side}^3 = {len(ps)} particle block (same spacing/jitter as the workload), "
+                      f"oracle cell-list restatement with OpenMP on {threads} threads, {dt:.1f} s"}
 
 
 def run_reference_arm(args):
