@@ -32,6 +32,7 @@ extern "C" {
 #define SPHB_ERR_CAPACITY 4  /* a fixed capacity was exceeded */
 
 #define SPHB_MAX_WALLS 16
+#define SPHB_MAX_SPHERES 16
 
 /* field_mask bits for sphb_download_aos / sphb_step_aos */
 #define SPHB_F_POS 1u
@@ -102,6 +103,15 @@ void sphb_destroy(sphb_engine* e);
  * `walls` points at `count` records of `stride` bytes whose first six floats are normal.xyz, center.xyz
  * (stride 32 for the reference's Wall, 24 for packed floats).  count <= SPHB_MAX_WALLS. */
 int sphb_set_walls(sphb_engine* e, const void* walls, size_t count, size_t stride);
+
+/* Rigid spheres as the `spheres` vector of update_forces / update_posvel / collision (SphUtils.cpp:163-166,
+ * 300-303, 331-334, 375-385; main.cpp:542-552).  `spheres` points at `count` records of `stride` bytes laid out
+ * like the reference's Sphere (44 B: pos, vel, accel, radius, mass); count <= SPHB_MAX_SPHERES, 0 removes them.
+ * The engine keeps them on the device: update_forces sets their acceleration to gravity, update_posvel
+ * integrates them, collision replays the particle-sphere velocity exchanges in the reference's serial order
+ * (ascending particle index, spheres in vector order).  sphb_get_spheres copies them back (synchronises). */
+int sphb_set_spheres(sphb_engine* e, const void* spheres, size_t count, size_t stride);
+int sphb_get_spheres(sphb_engine* e, void* spheres, size_t count, size_t stride);
 
 /* Host AoS -> device SoA.  `particles` points at n records of `stride` bytes laid out like the
  * reference's Particle (stride 52).  pos, vel, mass are taken; accel, density, pressure are taken too so

@@ -61,7 +61,7 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_count_nonfinite", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
+    "sphb_count_nonfinite", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
 ]
 
 _lib = None
@@ -90,6 +90,8 @@ def load_library() -> C.CDLL:
     L.sphb_destroy.argtypes = [vp]
     L.sphb_destroy.restype = None
     L.sphb_set_walls.argtypes = [vp, vp, sz, sz]
+    L.sphb_set_spheres.argtypes = [vp, vp, sz, sz]
+    L.sphb_get_spheres.argtypes = [vp, vp, sz, sz]
     L.sphb_upload_aos.argtypes = [vp, vp, sz, sz]
     L.sphb_download_aos.argtypes = [vp, vp, sz, sz, u32]
     for name in ("sphb_update_cells", "sphb_update_density", "sphb_update_forces", "sphb_update_posvel",
@@ -186,6 +188,18 @@ class Engine:
         else:
             w = np.ascontiguousarray(walls, np.float32).reshape(-1, 6)
             self._check(self.lib.sphb_set_walls(self.h, _ptr(w), len(w), 24))
+
+    def set_spheres(self, spheres: np.ndarray | None):
+        if spheres is None or len(spheres) == 0:
+            self._check(self.lib.sphb_set_spheres(self.h, None, 0, SPHERE.itemsize))
+            return
+        assert spheres.dtype == SPHERE and spheres.flags.c_contiguous
+        self._check(self.lib.sphb_set_spheres(self.h, _ptr(spheres), len(spheres), SPHERE.itemsize))
+
+    def get_spheres(self, spheres: np.ndarray):
+        assert spheres.dtype == SPHERE and spheres.flags.c_contiguous
+        self._check(self.lib.sphb_get_spheres(self.h, _ptr(spheres), len(spheres), SPHERE.itemsize))
+        return spheres
 
     def upload(self, particles: np.ndarray):
         assert particles.dtype == PARTICLE and particles.flags.c_contiguous

@@ -76,6 +76,9 @@ struct sphb_engine {
     DevBuf<int> row_groups; // exclusive scan of ceil(row length / kDT) over the (y,z) rows of cells (kMaxRows + 2)
     DevBuf<float> aos;      // staging for host AoS records
     DevBuf<float> scratch;  // eval_kernels, cells download
+    SphereDev* d_spheres = nullptr; // kMaxSpheres records + one int (contact count) behind them
+    int nspheres = 0;
+    DevBuf<int2> contacts;  // particle-sphere contacts: (original id, slot), unsorted then sorted (2 x capacity)
     DevBuf<int> mg_counts;  // multi-GPU pack: 3 per block, then totals[3] and recv_counts[4]
     int mg_blocks = 0;
     bool mg_pending = false; // sphb_mg_pack ran, sphb_mg_unpack has not committed yet
@@ -165,6 +168,7 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     e->rows = (e->c.cell >= e->c.h2) ? 9 : 25;
     CK(e->mask.reserve(want * (size_t)e->rows * 2));
     CK(e->vr.reserve(want));
+    if (e->nspheres) CK(e->contacts.reserve(2 * want));
     const int div = e->params.cell_x_div > 0 ? e->params.cell_x_div : 2;
     long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)div * (long long)(2 * want + 65536);
     if (mc > (1ll << 30)) mc = 1ll << 30;
@@ -246,6 +250,22 @@ auto force_kernel(int rows) {
     return rows == 9 ? k_force<kFused, kBBox, kAccel, 9, kDerive> : k_force<kFused, kBBox, kAccel, 25, kDerive>;
 }
 
+int* sphere_count_ptr(sphb_engine* e) { return (int*)(e->d_spheres + kMaxSpheres); }
+
+// particle-sphere contacts on the current state (after the wall pass): detect, order, replay
+int run_sphere_collision(sphb_engine* e) {
+    const int n = (int)e->n, cur = e->cur;
+    CK(e->contacts.reserve(2 * (e->posm[cur].cap ? e->posm[cur].cap : 1)));
+    int2* list = e->contacts.p;
+    int2* sorted = e->contacts.p + e->posm[cur].cap;
+    CK(cudaMemsetAsync(sphere_count_ptr(e), 0, sizeof(int), e->stream));
+    LAUNCH(e, k_sphere_detect, cdiv(n, 256), 256, 0, e->posm[cur].p, e->oid[cur].p, n, e->d_spheres, e->nspheres, list, sphere_count_ptr(e));
+    LAUNCH(e, k_sphere_rank, 148 * 4, 256, 0, list, sphere_count_ptr(e), sorted);
+    LAUNCH(e, k_sphere_serial, 1, 32, 0, e->posm[cur].p, e->vel[cur].p, sorted, sphere_count_ptr(e), e->d_spheres, e->nspheres);
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
 int check_ready(sphb_engine* e) {
     if (!e) return fail(SPHB_ERR_INVALID, "null engine");
     if (!e->have_state) return fail(SPHB_ERR_STATE, "no particles uploaded");
@@ -322,7 +342,8 @@ void sphb_destroy(sphb_engine* e) {
         e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
     }
     e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release(); e->vr.release();
-    e->cell_start.release(); e->block_sums.release(); e->row_groups.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release();
+    e->cell_start.release(); e->block_sums.release(); e->row_groups.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release(); e->contacts.release();
+    if (e->d_spheres) cudaFree(e->d_spheres);
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
     if (e->ev) {
@@ -349,6 +370,37 @@ int sphb_set_walls(sphb_engine* e, const void* walls, size_t count, size_t strid
         volatile float inv = 1.0f / sqrtf(s);
         for (int a = 0; a < 3; a++) e->c.wu[w][a] = f[a] * inv;
     }
+    return SPHB_OK;
+}
+
+int sphb_set_spheres(sphb_engine* e, const void* spheres, size_t count, size_t stride) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (count > SPHB_MAX_SPHERES) return fail(SPHB_ERR_CAPACITY, "at most %d spheres", SPHB_MAX_SPHERES);
+    if (count && (!spheres || stride < sizeof(SphereDev))) return fail(SPHB_ERR_INVALID, "spheres need >= 44-byte records");
+    int rc = use_device(e);
+    if (rc) return rc;
+    if (!e->d_spheres) CK(cudaMalloc((void**)&e->d_spheres, kMaxSpheres * sizeof(SphereDev) + 16));
+    SphereDev h[kMaxSpheres];
+    for (size_t j = 0; j < count; j++) memcpy(&h[j], (const char*)spheres + j * stride, sizeof(SphereDev));
+    if (count) {
+        CK(cudaMemcpyAsync(e->d_spheres, h, count * sizeof(SphereDev), cudaMemcpyHostToDevice, e->stream));
+        CK(cudaStreamSynchronize(e->stream)); // h lives on this stack frame
+    }
+    e->nspheres = (int)count;
+    return SPHB_OK;
+}
+
+int sphb_get_spheres(sphb_engine* e, void* spheres, size_t count, size_t stride) {
+    if (!e) return fail(SPHB_ERR_INVALID, "null engine");
+    if (count != (size_t)e->nspheres) return fail(SPHB_ERR_INVALID, "the engine holds %d spheres, not %zu", e->nspheres, count);
+    if (count && (!spheres || stride < sizeof(SphereDev))) return fail(SPHB_ERR_INVALID, "spheres need >= 44-byte records");
+    if (!count) return SPHB_OK;
+    int rc = use_device(e);
+    if (rc) return rc;
+    SphereDev h[kMaxSpheres];
+    CK(cudaMemcpyAsync(h, e->d_spheres, count * sizeof(SphereDev), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    for (size_t j = 0; j < count; j++) memcpy((char*)spheres + j * stride, &h[j], sizeof(SphereDev));
     return SPHB_OK;
 }
 
@@ -452,6 +504,7 @@ int sphb_update_density(sphb_engine* e) {
 int sphb_update_forces(sphb_engine* e) {
     int rc = check_ready(e);
     if (rc) return rc;
+    if (e->nspheres) LAUNCH(e, k_sphere_forces, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
     if (e->n == 0) return SPHB_OK;
     if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
     if (!e->mask_valid && (rc = run_density(e, false))) return rc;
@@ -467,6 +520,7 @@ int sphb_update_forces(sphb_engine* e) {
 int sphb_update_posvel(sphb_engine* e) {
     int rc = check_ready(e);
     if (rc) return rc;
+    if (e->nspheres) LAUNCH(e, k_sphere_posvel, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
     if (e->n == 0) return SPHB_OK;
     const int n = (int)e->n, cur = e->cur;
     LAUNCH(e, k_posvel, cdiv(n, 256), 256, 0, e->c, e->posm[cur].p, e->vel[cur].p, e->accel[cur].p, n);
@@ -485,6 +539,7 @@ int sphb_collision(sphb_engine* e) {
     const int n = (int)e->n, cur = e->cur;
     LAUNCH(e, k_collision, cdiv(n, 256), 256, 0, e->c, e->posm[cur].p, e->vel[cur].p, n);
     CK(cudaGetLastError());
+    if (e->nspheres && (rc = run_sphere_collision(e))) return rc;
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
@@ -528,6 +583,11 @@ int sphb_step(sphb_engine* e, int nsteps) {
         e->mask_valid = false;
         e->vr_valid = false;
         e->bbox_valid = bbox;
+        if (e->nspheres) { // the same order as step_scene: forces, posvel (spheres after particles), collision
+            LAUNCH(e, k_sphere_forces, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
+            LAUNCH(e, k_sphere_posvel, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
+            if ((rc = run_sphere_collision(e))) return rc;
+        }
         if (timed) {
             CK(cudaEventRecord(ev[3], e->stream));
             e->timed_steps++;

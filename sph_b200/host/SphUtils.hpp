@@ -85,24 +85,23 @@ public:
 
     void update_forces(std::vector<Particle>& particles, std::vector<Sphere>& spheres) {
         if (particles.empty() || !ensure()) return;
-        warn_spheres(spheres);
-        if (!push(particles)) return;
+        if (!spheres_in(spheres) || !push(particles)) return;
         if (!ok(sphb_update_forces(eng_))) return;
         pull(particles, SPHB_F_ACCEL);
+        spheres_out(spheres);
     }
 
     void update_posvel(std::vector<Particle>& particles, std::vector<Sphere>& spheres) {
         if (particles.empty() || !ensure()) return;
-        warn_spheres(spheres);
-        if (!push(particles)) return;
+        if (!spheres_in(spheres) || !push(particles)) return;
         if (!ok(sphb_update_posvel(eng_))) return;
         pull(particles, SPHB_F_POS | SPHB_F_VEL);
+        spheres_out(spheres);
     }
 
     void collision(std::vector<Particle>& particles, std::vector<Wall>& walls, std::vector<Sphere>& spheres) {
         if (particles.empty() || !ensure()) return;
-        warn_spheres(spheres);
-        if (!set_walls(walls)) return;
+        if (!set_walls(walls) || !spheres_in(spheres)) return;
         if (!push(particles)) return;
         if (!ok(sphb_collision(eng_))) return;
 #ifdef SPHB_SHIM_SYNC_ON_COLLISION
@@ -111,6 +110,7 @@ public:
 #else
         pull(particles, SPHB_F_POS | SPHB_F_VEL);
 #endif
+        spheres_out(spheres);
     }
 
     // step_scene (main.cpp:280-303) x nsteps through the fused fast path; not part of the reference's class.
@@ -169,12 +169,14 @@ private:
         float a[3] = {i.x, i.y, i.z}, b[3] = {j.x, j.y, j.z};
         ok(sphb_eval_kernels(eng_, a, b, 1, w, g, l));
     }
-    void warn_spheres(std::vector<Sphere>& spheres) {
-        static bool told = false;
-        if (!spheres.empty() && !told) {
-            fprintf(stderr, "sphb200: sphere coupling (SphUtils.cpp:375-385) is not built yet; spheres are ignored\n");
-            told = true;
-        }
+    // the reference mutates the caller's Sphere records in place: hand them to the engine, take them back
+    bool spheres_in(std::vector<Sphere>& spheres) {
+        size_t n = spheres.size() < SPHB_MAX_SPHERES ? spheres.size() : SPHB_MAX_SPHERES;
+        return ok(sphb_set_spheres(eng_, n ? &spheres[0] : 0, n, sizeof(Sphere)));
+    }
+    void spheres_out(std::vector<Sphere>& spheres) {
+        size_t n = spheres.size() < SPHB_MAX_SPHERES ? spheres.size() : SPHB_MAX_SPHERES;
+        if (n) ok(sphb_get_spheres(eng_, &spheres[0], n, sizeof(Sphere)));
     }
 };
 #endif

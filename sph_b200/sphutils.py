@@ -68,20 +68,29 @@ class SphUtils:
         self.engine.update_density()
         self._down(particles, F_DENSITY)
 
+    def _spheres_in(self, spheres):
+        self.engine.set_spheres(spheres)
+
+    def _spheres_out(self, spheres):
+        if spheres is not None and len(spheres):
+            self.engine.get_spheres(spheres)       # the reference mutates the caller's Sphere records in place
+
     def update_forces(self, particles, spheres=None):
-        _no_spheres(spheres)
+        self._spheres_in(spheres)
         self._up(particles)
         self.engine.update_forces()
         self._down(particles, F_ACCEL)
+        self._spheres_out(spheres)
 
     def update_posvel(self, particles, spheres=None):
-        _no_spheres(spheres)
+        self._spheres_in(spheres)
         self._up(particles)
         self.engine.update_posvel()
         self._down(particles, F_POS | F_VEL)
+        self._spheres_out(spheres)
 
     def collision(self, particles, walls, spheres=None):
-        _no_spheres(spheres)
+        self._spheres_in(spheres)
         key = walls.tobytes()
         if key != self._walls_key:
             self.engine.set_walls(walls)
@@ -93,16 +102,14 @@ class SphUtils:
         else:
             self.engine.download(particles, F_ALL)
             self._resident = False
+        self._spheres_out(spheres)
 
     # --- fused fast path: step_scene (main.cpp:280-303) x nsteps on host records
-    def step_scene(self, particles, walls, nsteps=1, mask=F_ALL):
+    def step_scene(self, particles, walls, nsteps=1, mask=F_ALL, spheres=None):
         key = walls.tobytes()
         if key != self._walls_key:
             self.engine.set_walls(walls)
             self._walls_key = key
+        self._spheres_in(spheres)
         self.engine.step_aos(particles, nsteps, mask)
-
-
-def _no_spheres(spheres):
-    if spheres is not None and len(spheres):
-        raise NotImplementedError("sphere coupling (SphUtils.cpp:375-385) is not built yet: SURVEY.md 8(f) row f3")
+        self._spheres_out(spheres)

@@ -462,3 +462,51 @@ def test_headless_cpp_driver(golden, mode):
     assert int(rows[10][7], 16) == int(g["fnv"][2])
     assert float(rows[20][3]) == pytest.approx(float(g["stats"][3][0]), abs=1e-3)    # mean rho after 20 steps
     assert float(rows[20][5]) == pytest.approx(float(g["stats"][3][2]), rel=1e-2)    # kinetic energy
+
+
+# --------------------------------------------------------------------------------------------------
+# rigid spheres (SphUtils.cpp:163-166, 300-303, 331-334, 375-385): serial semantics, bit-exact
+
+def _spheres(specs):
+    sp = np.zeros(len(specs), sph_b200.SPHERE)
+    for k, (pos, vel, radius, mass) in enumerate(specs):
+        sp[k]["pos"], sp[k]["vel"], sp[k]["radius"], sp[k]["mass"] = pos, vel, radius, mass
+    return sp
+
+
+def test_sphere_phases_bit_exact(oracle):
+    ps, walls = scenes.dam_break(16, 16, 16, stressed=True)
+    # two spheres inside the block (main.cpp:542-552 uses radius 0.1, mass 1.2); the second overlaps the first's contacts
+    sp = _spheres([((0.7, 0.7, 0.7), (0.0, 2.0, 0.0), 0.1, 1.2), ((0.8, 0.75, 0.7), (0.5, -1.0, 0.25), 0.25, 3.0)])
+    sph = SphUtils()
+    a, b, sa, sb = ps.copy(), ps.copy(), sp.copy(), sp.copy()
+    oracle.update_density(a, cells=True)
+    b[:] = a                                        # same rho, P into the force phase
+    oracle.update_forces(a, cells=True)
+    oracle.lib.orc_update_forces_spheres(sa.ctypes.data_as(__import__("ctypes").c_void_p), len(sa))
+    sph.update_forces(b, sb)
+    assert sa.tobytes() == sb.tobytes()             # sphere accel = gravity
+    b[:] = a
+    oracle.update_posvel(a, sa)
+    sph.update_posvel(b, sb)
+    assert a.tobytes() == b.tobytes() and sa.tobytes() == sb.tobytes()
+    oracle.collision(a, walls, sa)
+    sph.collision(b, walls, sb)
+    hit = np.linalg.norm(a["pos"] - sp[1]["pos"], axis=1) <= 0.36
+    assert hit.sum() > 50                           # many contacts: the replay order matters
+    assert a.tobytes() == b.tobytes(), "particle velocities after the sphere contacts differ"
+    assert sa.tobytes() == sb.tobytes(), "sphere velocities differ: contacts were not replayed in particle-index order"
+
+
+def test_sphere_fused_step_equals_phases():
+    ps, walls = scenes.dam_break(16, 16, 16, stressed=True)
+    sp = _spheres([((0.7, 1.2, 0.7), (0.0, -2.0, 0.0), 0.2, 1.2)])
+    a, b, sa, sb = ps.copy(), ps.copy(), sp.copy(), sp.copy()
+    s1, s2 = SphUtils(), SphUtils()
+    for _ in range(4):
+        s1.update_density(a); s1.update_forces(a, sa); s1.update_posvel(a, sa); s1.collision(a, walls, sa)
+    s2.step_scene(b, walls, nsteps=4, spheres=sb)
+    assert sa.tobytes() == sb.tobytes()
+    for f in ("pos", "vel", "accel", "density", "pressure"):
+        assert np.array_equal(a[f], b[f]), f
+    assert not np.array_equal(sa["vel"], sp["vel"])
