@@ -1,8 +1,10 @@
 // Headless driver: the reference's scene set-up and step loop (SPH/main.cpp initScene :555-559,
 // initParticles :490-505, addParticle :424-442, initWalls :508-540, step_scene :280-303) with every GL /
 // GLUT call left out, driving the engine through the drop-in SphUtils class exactly as main.cpp does.
-//   sph_headless [steps=20] [fused]
+//   sph_headless [steps=20] [fused|methods] [emit]
 // "fused" uses SphUtils::step_scene (one sphb_step_aos call per step) instead of the four methods.
+// "emit" switches the emitter of step_scene on (main.cpp:281-290, the Enter key): one particle per step from
+// rand(), until MAX_PARTICLES -- the particle vector grows between steps and the engine follows.
 // Prints particle count and, per reported step, mean density, kinetic energy and the FNV-1a-64 hash of the
 // position bits (the same hash tests/golden/default_scene.npz holds for the compiled reference).
 #include <stdint.h>
@@ -46,7 +48,18 @@ static void initScene() {
     walls.push_back(Wall(glm::vec3(0.0f, -1.0f, 0.0f), glm::vec3(0.0f, 1.0f, 0.0f), 1.0f, 1.0f));
 }
 
+static bool generateParticles = false;
+
 static void step_scene(bool fused) {
+    if (generateParticles) { // main.cpp:281-290
+        float x = -.2f + rand() / ((float)RAND_MAX / (-0.2f - 0.2f));
+        float y = 1.3f;
+        float z = -.2f + rand() / ((float)RAND_MAX / (-0.2f - 0.2f));
+        float xvel = -.2f + rand() / ((float)RAND_MAX / (-0.2f - 0.2f));
+        float zvel = -.2f + rand() / ((float)RAND_MAX / (-0.2f - 0.2f));
+        float yvel = -1.0f;
+        addParticle(glm::vec3(x, y, z), glm::vec3(xvel, yvel, zvel));
+    }
     if (fused) {
         sph.step_scene(particles, walls, 1);
         return;
@@ -74,6 +87,7 @@ static uint64_t fnv_pos() {
 int main(int argc, char** argv) {
     int steps = argc > 1 ? atoi(argv[1]) : 20;
     bool fused = argc > 2 && strcmp(argv[2], "fused") == 0;
+    generateParticles = argc > 3 && strcmp(argv[3], "emit") == 0;
     initScene();
     printf("particles %zu walls %zu\n", particles.size(), walls.size());
     if (!sph.engine()) return 2;
@@ -86,7 +100,8 @@ int main(int argc, char** argv) {
                 rho += q.density;
                 ke += 0.5 * q.mass * ((double)q.vel.x * q.vel.x + (double)q.vel.y * q.vel.y + (double)q.vel.z * q.vel.z);
             }
-            printf("step %d mean_rho %.6f ke %.6f fnv %016llx\n", s, rho / particles.size(), ke, (unsigned long long)fnv_pos());
+            printf("step %d mean_rho %.6f ke %.6f fnv %016llx n %zu\n", s, rho / particles.size(), ke, (unsigned long long)fnv_pos(),
+                   particles.size());
         }
     }
     return 0;

@@ -510,3 +510,15 @@ def test_sphere_fused_step_equals_phases():
     for f in ("pos", "vel", "accel", "density", "pressure"):
         assert np.array_equal(a[f], b[f]), f
     assert not np.array_equal(sa["vel"], sp["vel"])
+
+
+def test_headless_cpp_driver_emitter_grows_the_vector():
+    """main.cpp's emitter (:281-290, :441): one particle per step from rand() until MAX_PARTICLES = 1300."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "sph_b200", "host", "sph_headless")
+    out = subprocess.run([exe, "400", "methods", "emit"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    rows = {int(l.split()[1]): l.split() for l in out.stdout.strip().splitlines()[1:]}
+    assert int(rows[1][9]) == 973 and int(rows[100][9]) == 1072 and int(rows[400][9]) == 1300
+    assert all(np.isfinite(float(r[3])) for r in rows.values())
