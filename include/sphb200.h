@@ -80,7 +80,12 @@ typedef struct sphb_params {
                               (y,z) row are contiguous in memory, so a finer x pitch only trims the candidate run
                               from 3 cells to 2R + 2 cell_x.  0 => 2 (fastest measured on B200: finer pitches cost more in
                               the sort and in L1 wavefronts than they save in tests).  1 => cubic cells */
-    int32_t reserved[6];
+    int32_t laplacian_viscosity; /* 1 => update_forces also adds the reference's viscosity_forces term
+                              accel_i += lap_visc_coef * m_j / (rho_i rho_j) * lapW_ij * (v_i - v_j)   (SphUtils.cpp:244-290,
+                              277-278), on the full neighbourhood.  0 (default): off, as in the reference, whose call is
+                              commented out (SphUtils.cpp:175).  When on, sphb_step runs the phases unfused */
+    float lap_visc_coef;   /* 0.1f (SphUtils.cpp:277) */
+    int32_t reserved[4];
 } sphb_params;
 
 /* Fill *p with the reference's constants (main.cpp:30-41 and the literals of SphUtils.cpp). */

@@ -99,6 +99,13 @@ class Oracle:
         else:
             self.lib.orc_update_forces_allpairs(self.p, _vp(ps), C.c_size_t(len(ps)))
 
+    def viscosity_forces(self, ps, cells=False, threads=0):
+        """The dead viscosity_forces (SphUtils.cpp:244-290) on its full neighbourhood; adds into accel."""
+        if cells:
+            self.lib.orc_viscosity_forces_cells(self.p, _vp(ps), C.c_size_t(len(ps)), C.c_int(threads))
+        else:
+            self.lib.orc_viscosity_forces_allpairs(self.p, _vp(ps), C.c_size_t(len(ps)))
+
     def update_posvel(self, ps, spheres=None):
         ns = 0 if spheres is None else len(spheres)
         self.lib.orc_update_posvel(self.p, _vp(ps), C.c_size_t(len(ps)), _vp(spheres) if ns else None, C.c_size_t(ns))
@@ -224,6 +231,9 @@ class Reference:
         ns = 0 if spheres is None else len(spheres)
         self.lib.ref_collision(self.h, _vp(ps), C.c_size_t(len(ps)), _vp(walls), C.c_size_t(len(walls)),
                                _vp(spheres) if ns else None, C.c_size_t(ns))
+
+    def viscosity_forces(self, ps):
+        self.lib.ref_viscosity_forces(self.h, _vp(ps), C.c_size_t(len(ps)))
 
     def step(self, ps, walls, nsteps=1):
         self.lib.ref_step(self.h, _vp(ps), C.c_size_t(len(ps)), _vp(walls), C.c_size_t(len(walls)), C.c_int(nsteps))

@@ -125,6 +125,18 @@ void ref_step(void* s, void* particles, size_t n, const void* walls, size_t nw, 
     from_vec(v, particles);
 }
 
+// viscosity_forces (SphUtils.cpp:244-290) is private and its only call site is commented out (:175).  Exposed
+// so that the oracle's restatement of its pair body can be pinned: on a particle set that fits inside ONE of
+// the reference's 2h-wide cells, its half stencil {-1,0}^3 degenerates to "all pairs, ascending index".
+// Adds into accel, like the reference would.
+void ref_viscosity_forces(void* s, void* particles, size_t n) {
+    auto v = to_vec(particles, n);
+    SphUtils* u = static_cast<SphUtils*>(s);
+    u->update_cells(v);
+    u->viscosity_forces(v);
+    from_vec(v, particles);
+}
+
 // update_cells (SphUtils.cpp:8-47) with its private results exposed.  The caller must make sure the
 // reference's flat index (with its stray "+ny", SphUtils.cpp:43) stays inside nx*ny*nz, otherwise
 // the reference itself writes out of bounds; ref_cells_index_bound() tells.

@@ -176,6 +176,26 @@ void orc_update_forces_allpairs(const orc_params* p, orc_particle* ps, size_t n)
     }
 }
 
+/* SphUtils.cpp:277-278, the pair body of the dead viscosity_forces: accel_i += 0.1 m_j / (rho_i rho_j) lapW (v_i - v_j).
+ * (The sign spreads velocity differences instead of damping them; it is restated as written.) */
+static inline void viscosity_pair(const orc_params* p, const orc_particle* a, const orc_particle* b, float acc[3]) {
+    float temp = 0.1f * b->mass / (a->density * b->density) * orc_lap_kernel(p, a->pos, b->pos);
+    acc[0] += temp * (a->vel[0] - b->vel[0]);
+    acc[1] += temp * (a->vel[1] - b->vel[1]);
+    acc[2] += temp * (a->vel[2] - b->vel[2]);
+}
+
+/* viscosity_forces over ALL pairs in ascending index: what SphUtils.cpp:244-290 computes when every particle lies
+ * in one of its cells (pinned against the reference in that situation); adds into accel. */
+void orc_viscosity_forces_allpairs(const orc_params* p, orc_particle* ps, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        float acc[3] = {ps[i].accel[0], ps[i].accel[1], ps[i].accel[2]};
+        for (size_t j = 0; j < n; j++)
+            if (i != j) viscosity_pair(p, &ps[i], &ps[j], acc);
+        ps[i].accel[0] = acc[0]; ps[i].accel[1] = acc[1]; ps[i].accel[2] = acc[2];
+    }
+}
+
 /* Sphere side of update_forces (:163-166,300-303): accel = 0 then += (0,-1,0) */
 void orc_update_forces_spheres(orc_sphere* s, size_t ns) {
     for (size_t i = 0; i < ns; i++) {
@@ -479,6 +499,36 @@ void orc_update_forces_cells(const orc_params* p, orc_particle* ps, size_t n, in
             float acc[3] = {0.0f, 0.0f, 0.0f};
             acc[0] += 0.0f; acc[1] += -1.0f; acc[2] += 0.0f;
             for (int k = 0; k < cnt; k++) pressure_pair(p, &ps[i], &ps[buf[k]], acc);
+            acc_all[3 * i] = acc[0]; acc_all[3 * i + 1] = acc[1]; acc_all[3 * i + 2] = acc[2];
+        }
+        free(buf);
+    }
+    for (size_t i = 0; i < n; i++) memcpy(ps[i].accel, &acc_all[3 * i], 3 * sizeof(float));
+    free(acc_all);
+    cellctx_free(&c);
+}
+
+/* viscosity_forces over a cell list (ascending original index): bit-identical to the all-pairs loop, because a
+ * pair outside the support has lapW = 0.0f and adds +-0 */
+void orc_viscosity_forces_cells(const orc_params* p, orc_particle* ps, size_t n, int threads) {
+    if (n == 0) return;
+    cellctx c;
+    cellctx_init(&c, p, ps, n);
+    float* acc_all = (float*)malloc(sizeof(float) * 3 * n);
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel num_threads(threads)
+#endif
+    {
+        int cap = 512;
+        int* buf = (int*)malloc(sizeof(int) * cap);
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 256)
+#endif
+        for (long long i = 0; i < (long long)n; i++) {
+            int cnt = gather_sorted(&c, p, ps, (size_t)i, &buf, &cap);
+            float acc[3] = {ps[i].accel[0], ps[i].accel[1], ps[i].accel[2]};
+            for (int k = 0; k < cnt; k++) viscosity_pair(p, &ps[i], &ps[buf[k]], acc);
             acc_all[3 * i] = acc[0]; acc_all[3 * i + 1] = acc[1]; acc_all[3 * i + 2] = acc[2];
         }
         free(buf);

@@ -53,6 +53,7 @@ struct Consts {
     float dom_lo[3], dom_hi[3];
     int periodic[3];
     long long max_cells;
+    float lap_coef; // coefficient of the optional Laplacian viscosity (SphUtils.cpp:277), 0 when off
     float cell;   // cell edge in y and z
     float cell_x; // cell edge in x (cell / cell_x_div)
     int stencil_x;
@@ -845,6 +846,53 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         }
     }
     if (kFused && kBBox) bbox_block_commit(lo, hi, bbox);
+}
+
+// Optional: the reference's dead viscosity_forces (SphUtils.cpp:244-290; its call at :175 is commented out), on
+// the full neighbourhood:  accel_i += coef * m_j / (rho_i rho_j) * lapW_ij * (v_i - v_j),  lapW = 45/(pi h^6) (h - q)
+// (:84-95).  A separate pass over the neighbour masks that adds into accel; row by row, off the hot path.
+__global__ void __launch_bounds__(128) k_lap_viscosity(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                       const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
+                                                       const unsigned int* __restrict__ mask, float4* __restrict__ accel, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const GridDesc g = *gd;
+    const float4 pi = ldg4(posm + i), vi = ldg4(vel + i), ai = ldg4(aux + i);
+    int cx, cy, cz;
+    cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
+    const int nrows = (2 * g.stencil + 1) * (2 * g.stencil + 1);
+    float ax = 0.0f, ay = 0.0f, az = 0.0f;
+    auto pair = [&](int j) {
+        const float4 pj = ldg4(posm + j), vj = ldg4(vel + j), aj = ldg4(aux + j);
+        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        const float s = fmaf(-sqrtf(d2), c.inv_h, c.h);      // h - q
+        const float t = c.lap_coef * pj.w * ai.w * aj.w * s; // times Kl after the sum
+        ax = fmaf(t, vi.x - vj.x, ax);
+        ay = fmaf(t, vi.y - vj.y, ay);
+        az = fmaf(t, vi.z - vj.z, az);
+    };
+    for (int r = 0; r < nrows; r++) {
+        int jb, je;
+        row_run(g, cell_start, cx, cy, cz, r, jb, je);
+        for (int w = 0; w < 2; w++) {
+            unsigned int m = mask[(size_t)(2 * r + w) * n + i];
+            while (m) {
+                pair(jb + 32 * w + __ffs((int)m) - 1);
+                m &= m - 1;
+            }
+        }
+        for (int j = jb + kMaskBits; j < je; j++) { // crowded run: beyond the mask
+            const float4 pj = ldg4(posm + j);
+            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < c.R2 && j != i) pair(j);
+        }
+    }
+    float4 a = accel[i];
+    a.x = fmaf(c.Kl, ax, a.x);
+    a.y = fmaf(c.Kl, ay, a.y);
+    a.z = fmaf(c.Kl, az, a.z);
+    accel[i] = a;
 }
 
 // Phase kernels for the method-by-method API (update_posvel, collision), in place.

@@ -144,6 +144,7 @@ void build_consts(sphb_engine* e) {
         c.dom_hi[a] = p.domain_hi[a];
         c.periodic[a] = p.periodic[a];
     }
+    c.lap_coef = p.laplacian_viscosity ? p.lap_visc_coef : 0.0f;
     c.cell = p.cell_size > 0.0f ? p.cell_size : c.h2;
     const int div = p.cell_x_div > 0 ? p.cell_x_div : 2;
     c.cell_x = c.cell / (float)div;
@@ -296,6 +297,8 @@ void sphb_default_params(sphb_params* p) {
     p->domain_mode = SPHB_DOMAIN_BBOX;
     p->max_cells = 0;
     p->write_accel = 1;
+    p->laplacian_viscosity = 0; // the reference's call is commented out (SphUtils.cpp:175)
+    p->lap_visc_coef = 0.1f;    // SphUtils.cpp:277
 }
 
 const char* sphb_last_error(void) { return g_err; }
@@ -513,6 +516,9 @@ int sphb_update_forces(sphb_engine* e) {
     auto kfn = e->vr_valid ? force_kernel<false, false, true, true>(e->rows) : force_kernel<false, false, true, false>(e->rows);
     LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p,
            e->aux[cur].p, e->vr.p, e->mask.p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
+    if (e->params.laplacian_viscosity)
+        LAUNCH(e, k_lap_viscosity, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
+               e->mask.p, e->accel[cur].p, n);
     CK(cudaGetLastError());
     return SPHB_OK;
 }
@@ -555,6 +561,12 @@ int sphb_step(sphb_engine* e, int nsteps) {
     const int n = (int)e->n;
     const bool bbox = !e->c.domain_fixed;
     const bool acc = e->params.write_accel != 0;
+    if (e->params.laplacian_viscosity) { // optional extra force pass: run the phases one by one
+        for (int s = 0; s < nsteps; s++)
+            if ((rc = sphb_update_density(e)) || (rc = sphb_update_forces(e)) || (rc = sphb_update_posvel(e)) || (rc = sphb_collision(e)))
+                return rc;
+        return SPHB_OK;
+    }
     for (int s = 0; s < nsteps; s++) {
         const bool timed = e->timing && e->timed_steps < sphb_engine::kMaxTimed;
         cudaEvent_t* ev = timed ? e->ev + 4 * e->timed_steps : nullptr;

@@ -522,3 +522,37 @@ def test_headless_cpp_driver_emitter_grows_the_vector():
     rows = {int(l.split()[1]): l.split() for l in out.stdout.strip().splitlines()[1:]}
     assert int(rows[1][9]) == 973 and int(rows[100][9]) == 1072 and int(rows[400][9]) == 1300
     assert all(np.isfinite(float(r[3])) for r in rows.values())
+
+
+# --------------------------------------------------------------------------------------------------
+# optional Laplacian viscosity (SphUtils.cpp:244-290; dead in the reference, off by default)
+
+def test_laplacian_viscosity_flag(oracle, golden):
+    g = golden("block4096.npz")
+    ps = g["density"].copy()                       # reference rho, P
+    want = ps.copy()
+    oracle.update_forces(want, cells=True)
+    base = want["accel"].copy()
+    oracle.viscosity_forces(want, cells=True)
+    with sph_b200.Engine(laplacian_viscosity=1) as e:
+        e.upload(ps)
+        e.update_forces()
+        e.download(ps, sph_b200.F_ACCEL)
+    extra = np.abs(want["accel"] - base).max()
+    assert extra > 0.05                             # the term is there ...
+    scale = sum_abs_terms(oracle, want)
+    _, normd = accel_errors(ps["accel"], want["accel"], scale)
+    assert normd <= ACC_TOL                         # ... and matches the restated reference term
+    # default: off, like the reference
+    ps2 = g["density"].copy()
+    with sph_b200.Engine() as e:
+        e.upload(ps2); e.update_forces(); e.download(ps2, sph_b200.F_ACCEL)
+    _, n2 = accel_errors(ps2["accel"], base, scale)
+    assert n2 <= ACC_TOL
+    # fused entry point with the flag on == the phases
+    a, b = g["initial"].copy(), g["initial"].copy()
+    with sph_b200.Engine(laplacian_viscosity=1) as e1, sph_b200.Engine(laplacian_viscosity=1) as e2:
+        e1.set_walls(g["walls"]); e2.set_walls(g["walls"])
+        e1.upload(a); e1.update_density(); e1.update_forces(); e1.update_posvel(); e1.collision(); e1.download(a, F_ALL)
+        e2.step_aos(b, 1)
+    assert a.tobytes() == b.tobytes()

@@ -113,3 +113,17 @@ def test_update_cells_restatement(oracle, reference):
     n2, bbox2, dims2, cell2 = reference.update_cells(ps)
     assert n1 == n2 == 18 and same_bits(bbox1, bbox2) and same_bits(dims1, dims2) and same_bits(cell1, cell2)
     assert sorted(set(cell1.tolist())) == [0, 1, 8, 9]
+
+
+def test_dead_viscosity_forces_pair_body(oracle, reference):
+    """viscosity_forces (SphUtils.cpp:244-290) never runs in the reference (:175) and scans only half a stencil of
+    2h-wide cells; on a block that fits inside ONE such cell it degenerates to all pairs in ascending index, which
+    pins the oracle's restatement of its pair body (:277-278) and of lap_kernel (:84-95)."""
+    ps, _ = scenes.dam_break(8, 8, 8, stressed=True)          # 0.68 wide < 2h = 0.9
+    oracle.update_density(ps); oracle.update_forces(ps)
+    a, b, c = ps.copy(), ps.copy(), ps.copy()
+    oracle.viscosity_forces(a)
+    reference.viscosity_forces(b)
+    oracle.viscosity_forces(c, cells=True, threads=2)
+    assert same_bits(a, b) and same_bits(a, c)
+    assert np.abs(a["accel"] - ps["accel"]).max() > 0.05
