@@ -213,6 +213,10 @@ typedef struct sphb_slab {
     float halo;               /* ghost width; >= 2*h*h for the single-exchange scheme */
     int32_t has_left, has_right;
     float shift_left, shift_right; /* added to x of records sent that way: +-period across a periodic seam, else 0 */
+    int32_t periodic_y, periodic_z; /* periodic box in y / z (extension: the reference has only planes).  Owned particles
+                                  are wrapped into [lo, lo+len) and those within `halo` of a periodic face are copied as
+                                  ghost images shifted by the period, so the kernels need no minimum-image logic */
+    float ylo, ylen, zlo, zlen;
 } sphb_slab;
 
 /* Bytes of a message buffer that can carry `capacity` particles. */

@@ -36,7 +36,8 @@ class Slab(C.Structure):
     """struct sphb_slab (include/sphb200.h)."""
 
     _fields_ = [("lo", C.c_float), ("hi", C.c_float), ("halo", C.c_float), ("has_left", C.c_int32), ("has_right", C.c_int32),
-                ("shift_left", C.c_float), ("shift_right", C.c_float)]
+                ("shift_left", C.c_float), ("shift_right", C.c_float), ("periodic_y", C.c_int32), ("periodic_z", C.c_int32),
+                ("ylo", C.c_float), ("ylen", C.c_float), ("zlo", C.c_float), ("zlen", C.c_float)]
 
 
 class Params(C.Structure):

@@ -1130,61 +1130,93 @@ struct Slab {
     float lo, hi, halo;
     int has_left, has_right;
     float shift_left, shift_right; // added to x of a record sent that way (periodic seam), else 0
+    int per_y, per_z;              // periodic in y / z over [ylo, ylo + ylen) / [zlo, zlo + zlen)
+    float ylo, ylen, zlo, zlen;
 };
 
-constexpr int kMgThreads = 256;
+constexpr int kMgThreads = 256; // == kScanThreads: block_exclusive_scan is reused
 
-__device__ __forceinline__ void mg_classify(const Slab& s, const float4& p, const float4& v, bool& keep, bool& left, bool& right) {
-    const bool owned = v.w != 0.0f;
-    const float x = p.x;
-    keep = owned && x >= s.lo - s.halo && x < s.hi + s.halo;
-    left = owned && s.has_left && x < s.lo + s.halo;
-    right = owned && s.has_right && x >= s.hi - s.halo;
+// Periodic y / z are handled HERE and nowhere else: an owned particle is wrapped back into the box, and if it lies
+// within `halo` of a periodic face it is emitted once more per face (and once for the edge) shifted by the period,
+// as a ghost image.  The density / force kernels never see a periodic boundary -- only more ghosts.
+struct MgItem {
+    float4 p, v;      // wrapped position+mass, velocity (+flag)
+    int nimg;         // 1, 2 or 4 records: (0,0), (dy,0), (0,dz), (dy,dz)
+    float dy, dz;     // image shifts (0 if not near that face)
+    bool keep, left, right;
+};
+
+__device__ __forceinline__ float mg_wrap(float x, float lo, float len) {
+    x = x - len * floorf((x - lo) / len);
+    return x >= lo + len ? lo : x; // rounding can land exactly on the upper face
 }
 
-// pass 1: per-block counts of (keep, left, right)
+__device__ __forceinline__ MgItem mg_classify(const Slab& s, float4 p, const float4& v) {
+    MgItem it;
+    const bool owned = v.w != 0.0f;
+    it.dy = it.dz = 0.0f;
+    if (s.per_y) {
+        p.y = mg_wrap(p.y, s.ylo, s.ylen);
+        it.dy = p.y < s.ylo + s.halo ? s.ylen : (p.y >= s.ylo + s.ylen - s.halo ? -s.ylen : 0.0f);
+    }
+    if (s.per_z) {
+        p.z = mg_wrap(p.z, s.zlo, s.zlen);
+        it.dz = p.z < s.zlo + s.halo ? s.zlen : (p.z >= s.zlo + s.zlen - s.halo ? -s.zlen : 0.0f);
+    }
+    it.p = p;
+    it.v = v;
+    it.nimg = (it.dy != 0.0f ? 2 : 1) * (it.dz != 0.0f ? 2 : 1);
+    const float x = p.x;
+    it.keep = owned && x >= s.lo - s.halo && x < s.hi + s.halo;
+    it.left = owned && s.has_left && x < s.lo + s.halo;
+    it.right = owned && s.has_right && x >= s.hi - s.halo;
+    return it;
+}
+
+__device__ __forceinline__ float4 mg_image(const MgItem& it, int img, float xshift) {
+    // image order: base, y-image, z-image, edge image (only those that exist)
+    const bool sy = it.dy != 0.0f && (img == 1 || img == 3);
+    const bool sz = it.dz != 0.0f && ((it.dy != 0.0f) ? (img >= 2) : (img == 1));
+    return make_float4(it.p.x + xshift, sy ? it.p.y + it.dy : it.p.y, sz ? it.p.z + it.dz : it.p.z, it.p.w);
+}
+
+__device__ __forceinline__ bool mg_inside(const Slab& s, const float4& p) {
+    return p.x >= s.lo && p.x < s.hi && (!s.per_y || (p.y >= s.ylo && p.y < s.ylo + s.ylen)) &&
+           (!s.per_z || (p.z >= s.zlo && p.z < s.zlo + s.zlen));
+}
+
+// pass 1: per-block record counts of (keep, left, right)
 __global__ void __launch_bounds__(kMgThreads) k_mg_count(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
                                                          int* __restrict__ block_counts) {
     const int i = blockIdx.x * kMgThreads + threadIdx.x;
-    bool keep = false, left = false, right = false;
-    if (i < n) mg_classify(s, posm[i], vel[i], keep, left, right);
-    const int ck = __syncthreads_count(keep), cl = __syncthreads_count(left), cr = __syncthreads_count(right);
-    if (threadIdx.x == 0) {
-        block_counts[3 * blockIdx.x] = ck;
-        block_counts[3 * blockIdx.x + 1] = cl;
-        block_counts[3 * blockIdx.x + 2] = cr;
+    int c[3] = {0, 0, 0};
+    if (i < n) {
+        const MgItem it = mg_classify(s, posm[i], vel[i]);
+        c[0] = it.keep ? it.nimg : 0;
+        c[1] = it.left ? it.nimg : 0;
+        c[2] = it.right ? it.nimg : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        int tot;
+        block_exclusive_scan(c[k], &tot);
+        if (threadIdx.x == 0) block_counts[3 * blockIdx.x + k] = tot;
     }
 }
 
 // pass 2: one block turns the per-block counts into exclusive offsets (3 interleaved streams) and totals
 __global__ void __launch_bounds__(kMgThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int* __restrict__ totals) {
-    __shared__ int s_part[3][kMgThreads];
     int carry[3] = {0, 0, 0};
     for (int base = 0; base < nblocks; base += kMgThreads) {
         const int b = base + threadIdx.x;
-        int v[3];
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            v[k] = b < nblocks ? block_counts[3 * b + k] : 0;
-            s_part[k][threadIdx.x] = v[k];
+            const int v = b < nblocks ? block_counts[3 * b + k] : 0;
+            int tot;
+            const int ex = block_exclusive_scan(v, &tot);
+            if (b < nblocks) block_counts[3 * b + k] = carry[k] + ex;
+            carry[k] += tot;
         }
-        __syncthreads();
-        // Hillis-Steele inclusive scan over the chunk, three streams at once
-        for (int o = 1; o < kMgThreads; o <<= 1) {
-            int t[3];
-#pragma unroll
-            for (int k = 0; k < 3; k++) t[k] = threadIdx.x >= o ? s_part[k][threadIdx.x - o] : 0;
-            __syncthreads();
-#pragma unroll
-            for (int k = 0; k < 3; k++) s_part[k][threadIdx.x] += t[k];
-            __syncthreads();
-        }
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-            if (b < nblocks) block_counts[3 * b + k] = carry[k] + s_part[k][threadIdx.x] - v[k];
-            carry[k] += s_part[k][kMgThreads - 1];
-        }
-        __syncthreads();
     }
     if (threadIdx.x < 3) totals[threadIdx.x] = carry[threadIdx.x];
 }
@@ -1192,44 +1224,35 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_scan(int* __restrict__ block_
 // pass 3: write.  keep -> (posm_out, vel_out) with the ownership flag refreshed; left/right -> messages.
 __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
                                                          const int* __restrict__ block_offsets, const int* __restrict__ totals,
-                                                         float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                         float4* __restrict__ posm_out, float4* __restrict__ vel_out, int out_capacity,
                                                          float4* __restrict__ msg_left, float4* __restrict__ msg_right, int capacity) {
-    __shared__ int s_warp[3][kMgThreads / 32];
     const int i = blockIdx.x * kMgThreads + threadIdx.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    bool f[3] = {false, false, false};
-    float4 p = make_float4(0, 0, 0, 0), v = p;
-    if (i < n) {
-        p = posm[i];
-        v = vel[i];
-        mg_classify(s, p, v, f[0], f[1], f[2]);
-    }
-    int rank[3];
+    MgItem it;
+    it.keep = it.left = it.right = false;
+    it.nimg = 0;
+    if (i < n) it = mg_classify(s, posm[i], vel[i]);
+    int off[3];
+    const int cnt[3] = {it.keep ? it.nimg : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0};
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-        const unsigned b = __ballot_sync(0xffffffffu, f[k]);
-        rank[k] = __popc(b & ((1u << lane) - 1));
-        if (lane == 0) s_warp[k][warp] = __popc(b);
+        int tot;
+        off[k] = block_exclusive_scan(cnt[k], &tot) + block_offsets[3 * blockIdx.x + k];
     }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-        int off = block_offsets[3 * blockIdx.x + k];
-        for (int w = 0; w < warp; w++) off += s_warp[k][w];
-        rank[k] += off;
+    for (int img = 0; img < cnt[0]; img++) {
+        if (off[0] + img >= out_capacity) break;
+        const float4 q = mg_image(it, img, 0.0f);
+        posm_out[off[0] + img] = q;
+        vel_out[off[0] + img] = make_float4(it.v.x, it.v.y, it.v.z, (img == 0 && mg_inside(s, q)) ? 1.0f : 0.0f);
     }
-    if (f[0]) {
-        const bool inside = p.x >= s.lo && p.x < s.hi;
-        posm_out[rank[0]] = p;
-        vel_out[rank[0]] = make_float4(v.x, v.y, v.z, inside ? 1.0f : 0.0f);
+    for (int img = 0; img < cnt[1]; img++) {
+        if (off[1] + img >= capacity) break;
+        msg_left[2 + 2 * (off[1] + img)] = mg_image(it, img, s.shift_left);
+        msg_left[3 + 2 * (off[1] + img)] = it.v;
     }
-    if (f[1] && rank[1] < capacity) {
-        msg_left[2 + 2 * rank[1]] = make_float4(p.x + s.shift_left, p.y, p.z, p.w);
-        msg_left[3 + 2 * rank[1]] = v;
-    }
-    if (f[2] && rank[2] < capacity) {
-        msg_right[2 + 2 * rank[2]] = make_float4(p.x + s.shift_right, p.y, p.z, p.w);
-        msg_right[3 + 2 * rank[2]] = v;
+    for (int img = 0; img < cnt[2]; img++) {
+        if (off[2] + img >= capacity) break;
+        msg_right[2 + 2 * (off[2] + img)] = mg_image(it, img, s.shift_right);
+        msg_right[3 + 2 * (off[2] + img)] = it.v;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) { // headers: count, capacity
         if (msg_left) msg_left[0] = make_float4(__int_as_float(s.has_left ? totals[1] : 0), __int_as_float(capacity), 0.0f, 0.0f);
@@ -1250,9 +1273,8 @@ __global__ void __launch_bounds__(256) k_mg_append(Slab s, const float4* __restr
     for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < count; r += gridDim.x * blockDim.x) {
         if (base + r >= out_capacity) break;
         const float4 p = msg[2 + 2 * r], v = msg[3 + 2 * r];
-        const bool inside = p.x >= s.lo && p.x < s.hi;
         posm_out[base + r] = p;
-        vel_out[base + r] = make_float4(v.x, v.y, v.z, inside ? 1.0f : 0.0f);
+        vel_out[base + r] = make_float4(v.x, v.y, v.z, mg_inside(s, p) ? 1.0f : 0.0f);
     }
 }
 

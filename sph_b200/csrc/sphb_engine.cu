@@ -809,10 +809,14 @@ extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_lef
     if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
     if ((slab->has_left && !msg_left) || (slab->has_right && !msg_right)) return fail(SPHB_ERR_INVALID, "missing message buffer");
     if (capacity > 0x3fffffffu) return fail(SPHB_ERR_CAPACITY, "message capacity too large");
+    if ((slab->periodic_y && !(slab->ylen >= 2.0f * slab->halo)) || (slab->periodic_z && !(slab->zlen >= 2.0f * slab->halo)))
+        return fail(SPHB_ERR_INVALID, "a periodic axis must be at least two halos long");
     Slab s;
     s.lo = slab->lo; s.hi = slab->hi; s.halo = slab->halo;
     s.has_left = slab->has_left; s.has_right = slab->has_right;
     s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
+    s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
+    s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
     const int n = (int)e->n, cur = e->cur, nxt = cur ^ 1;
     const int nb = n ? cdiv(n, kMgThreads) : 1;
     CK(e->mg_counts.reserve((size_t)3 * nb + 16));
@@ -820,8 +824,9 @@ extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_lef
     int* totals = e->mg_counts.p + 3 * nb;
     LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p);
     LAUNCH(e, k_mg_scan, 1, kMgThreads, 0, e->mg_counts.p, nb, totals);
+    const int out_cap = (int)(e->posm[nxt].cap < 0x7fffffffu ? e->posm[nxt].cap : 0x7fffffffu);
     LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, e->posm[nxt].p,
-           e->vel[nxt].p, (float4*)msg_left, (float4*)msg_right, (int)capacity);
+           e->vel[nxt].p, out_cap, (float4*)msg_left, (float4*)msg_right, (int)capacity);
     CK(cudaGetLastError());
     e->mg_pending = true;
     return SPHB_OK;
@@ -836,6 +841,8 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     s.lo = slab->lo; s.hi = slab->hi; s.halo = slab->halo;
     s.has_left = slab->has_left; s.has_right = slab->has_right;
     s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
+    s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
+    s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
     const int nxt = e->cur ^ 1;
     int* totals = e->mg_counts.p + 3 * e->mg_blocks;
     int* recv = totals + 4;

@@ -28,23 +28,32 @@ def support_radius(h=0.45) -> float:
     return float(np.float32(h) * np.float32(h))
 
 
-def make_slab(rank: int, world: int, bounds, halo: float, period: float | None = None) -> capi.Slab:
-    """bounds: world+1 increasing x values; the outer two are replaced by -inf/+inf unless periodic."""
+def make_slab(rank: int, world: int, bounds, halo: float, period: float | None = None, yz_box=None) -> capi.Slab:
+    """bounds: world+1 increasing x values; the outer two are replaced by -inf/+inf unless x is periodic
+    (period = the x length of the whole box; with one rank the rank is then its own neighbour on both sides).
+    yz_box = ((ylo, ylen) or None, (zlo, zlen) or None) makes y and/or z periodic (ghost images, see sphb_slab)."""
     s = capi.Slab()
     periodic = period is not None
     s.lo = float(bounds[rank]) if (rank > 0 or periodic) else -math.inf
     s.hi = float(bounds[rank + 1]) if (rank < world - 1 or periodic) else math.inf
     s.halo = float(halo)
-    s.has_left = int(rank > 0 or (periodic and world > 1))
-    s.has_right = int(rank < world - 1 or (periodic and world > 1))
+    s.has_left = int(rank > 0 or periodic)
+    s.has_right = int(rank < world - 1 or periodic)
     s.shift_left = float(period) if (periodic and rank == 0) else 0.0
     s.shift_right = -float(period) if (periodic and rank == world - 1) else 0.0
+    if yz_box is not None:
+        yb, zb = yz_box
+        if yb is not None:
+            s.periodic_y, s.ylo, s.ylen = 1, float(yb[0]), float(yb[1])
+        if zb is not None:
+            s.periodic_z, s.zlo, s.zlen = 1, float(zb[0]), float(zb[1])
     return s
 
 
 def neighbours(rank: int, world: int, periodic: bool = False):
-    left = rank - 1 if rank > 0 else (world - 1 if periodic and world > 1 else None)
-    right = rank + 1 if rank < world - 1 else (0 if periodic and world > 1 else None)
+    """(left, right) ranks; with a periodic x a lone rank is its own neighbour."""
+    left = rank - 1 if rank > 0 else (world - 1 if periodic else None)
+    right = rank + 1 if rank < world - 1 else (0 if periodic else None)
     return left, right
 
 
@@ -57,7 +66,13 @@ def quantile_bounds(x: np.ndarray, world: int, cell: float, lo: float, hi: float
 
 def exchange(dist, send_left, send_right, recv_left, recv_right, left, right):
     """Post the (at most) four point-to-point operations of one halo exchange and wait for them.
-    Works on any backend (NCCL on device tensors, gloo on CPU tensors in the tests)."""
+    Works on any backend (NCCL on device tensors, gloo on CPU tensors in the tests).  A rank that is its own
+    neighbour (one rank, periodic x) copies locally."""
+    me = dist.get_rank() if dist is not None and dist.is_initialized() else 0
+    if left == me and right == me:       # world size 1, periodic x
+        recv_left.copy_(send_right)
+        recv_right.copy_(send_left)
+        return
     ops = []
     if right is not None:
         ops.append(dist.P2POp(dist.isend, send_right, right))
