@@ -50,6 +50,9 @@ WORKLOADS = {
     "drop16m": "block drop into tank, 16,777,216 particles (config 4)",
     "drop2m": "block drop into tank, 2,097,152 particles (config 4 at scale 2)",
     "drop256k": "block drop into tank, 262,144 particles (config 4 at scale 4)",
+    "periodic16m": "weak-scaling periodic box, 16,777,216 particles per GPU (config 5)",
+    "periodic2m": "weak-scaling periodic box, 2,097,152 particles per GPU (config 5 at scale 2)",
+    "periodic256k": "weak-scaling periodic box, 262,144 particles per GPU (config 5 at scale 4)",
 }
 
 
@@ -212,7 +215,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
+    if world > 1 or args.workload.startswith("periodic"):
         from sph_b200 import multigpu
         return multigpu.bench_main(args, world, rank, local)
     if not torch.cuda.is_available():

@@ -1246,12 +1246,17 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, const float4* _
     }
     for (int img = 0; img < cnt[1]; img++) {
         if (off[1] + img >= capacity) break;
-        msg_left[2 + 2 * (off[1] + img)] = mg_image(it, img, s.shift_left);
+        float4 q = mg_image(it, img, s.shift_left);
+        // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
+        if (s.shift_left != 0.0f && it.p.x < s.lo) q.x = fminf(q.x, nextafterf(s.lo + s.shift_left, -INFINITY));
+        msg_left[2 + 2 * (off[1] + img)] = q;
         msg_left[3 + 2 * (off[1] + img)] = it.v;
     }
     for (int img = 0; img < cnt[2]; img++) {
         if (off[2] + img >= capacity) break;
-        msg_right[2 + 2 * (off[2] + img)] = mg_image(it, img, s.shift_right);
+        float4 q = mg_image(it, img, s.shift_right);
+        if (s.shift_right != 0.0f && it.p.x >= s.hi) q.x = fmaxf(q.x, s.hi + s.shift_right);
+        msg_right[2 + 2 * (off[2] + img)] = q;
         msg_right[3 + 2 * (off[2] + img)] = it.v;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) { // headers: count, capacity

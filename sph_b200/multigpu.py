@@ -163,29 +163,69 @@ def bench_main(args, world, rank, local):
     from . import scenes
 
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    scale = {"drop16m": 1, "drop2m": 2, "drop256k": 4}.get(args.workload)
-    if scale is None:
-        raise SystemExit("multi-GPU bench runs the block-drop workloads (drop16m / drop2m / drop256k)")
-    section = 256 // scale * 0.1                     # x-length of one tank section = one GPU's share
-    ps = scenes.block_drop_section(rank, world, scale=scale)
-    walls = scenes.tank_walls(section * world + 0.2, section + 0.2)
-    n_own = len(ps)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     R = support_radius()
     halo = 2.0 * R * 1.001
-    bounds = [0.1 + section * r for r in range(world + 1)]
-    slab = make_slab(rank, world, bounds, halo)
-    left, right = neighbours(rank, world)
-    top = 0.1 + (192 + 256) // scale * 0.1 + 0.3 + 1.0
-    dlo = (bounds[rank] - halo - 0.35, -0.25, -0.25)
-    dhi = (bounds[rank + 1] + halo + 0.35, top, section + 0.45)
-    eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi,
-                      write_accel=0 if args.no_accel else 1)
-    eng.set_walls(walls)
-    face = (section + 0.2) * (192 // scale * 0.1 + 0.5) * 1100.0      # particles per unit x near a face (upper bound)
-    capacity = int(face * halo * 2.0) + 4096
-    eng.reserve(n_own + 2 * capacity)
+    periodic = args.workload.startswith("periodic")
+    if periodic:
+        # config 5: 256^3/scale^3 particles per GPU in a fully periodic box, G boxes side by side in x; no gravity, no walls
+        scale = {"periodic16m": 1, "periodic2m": 2, "periodic256k": 4}[args.workload]
+        side = 256 // scale
+        L = side * 0.1
+        pos, vel = scenes.lattice_block(side, side, side, 0.1, (0.05 + L * rank, 0.05, 0.05), seed=1234 + rank, jitter=0.2, vel_amp=0.5)
+        ps = scenes.make_particles(pos, vel)
+        del pos, vel
+        walls = None
+        bounds = [L * r for r in range(world + 1)]
+        slab = make_slab(rank, world, bounds, halo, period=L * world, yz_box=((0.0, L), (0.0, L)))
+        left, right = neighbours(rank, world, periodic=True)
+        m = halo + 0.35
+        dlo, dhi = (bounds[rank] - m, -m, -m), (bounds[rank + 1] + m, L + m, L + m)
+        eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi, gravity=(0.0, 0.0, 0.0),
+                          write_accel=0 if args.no_accel else 1)
+        n_own = len(ps)
+        capacity = int((L + 2 * halo) ** 2 * 1100.0 * halo * 1.6) + 4096
+        eng.reserve(int(n_own * ((L + 2 * halo) / L) ** 3 * 1.08) + 2 * capacity)
+        what = f", periodic box {L:.1f}^3 per GPU ({world} side by side in x), gravity off, no walls"
+    else:
+        scale = {"drop16m": 1, "drop2m": 2, "drop256k": 4}.get(args.workload)
+        if scale is None:
+            raise SystemExit("multi-GPU bench runs the block-drop (drop16m / drop2m / drop256k) and periodic workloads")
+        section = 256 // scale * 0.1                     # x-length of one tank section = one GPU's share
+        ps = scenes.block_drop_section(rank, world, scale=scale)
+        walls = scenes.tank_walls(section * world + 0.2, section + 0.2)
+        n_own = len(ps)
+        bounds = [0.1 + section * r for r in range(world + 1)]
+        slab = make_slab(rank, world, bounds, halo)
+        left, right = neighbours(rank, world)
+        top = 0.1 + (192 + 256) // scale * 0.1 + 0.3 + 1.0
+        dlo = (bounds[rank] - halo - 0.35, -0.25, -0.25)
+        dhi = (bounds[rank + 1] + halo + 0.35, top, section + 0.45)
+        eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi,
+                          write_accel=0 if args.no_accel else 1)
+        eng.set_walls(walls)
+        face = (section + 0.2) * (192 // scale * 0.1 + 0.5) * 1100.0      # particles per unit x near a face (upper bound)
+        capacity = int(face * halo * 2.0) + 4096
+        eng.reserve(n_own + 2 * capacity)
+        what = f", one tank section per GPU ({world} sections side by side)"
     sr = SlabRank(eng, slab, capacity, local)
+
+    class _Solo:  # world size 1: no process group; the only "collectives" are identities
+        ReduceOp = dist.ReduceOp
+        P2POp, isend, irecv, batch_isend_irecv = dist.P2POp, dist.isend, dist.irecv, dist.batch_isend_irecv
+        @staticmethod
+        def is_initialized(): return False
+        @staticmethod
+        def get_rank(): return 0
+        @staticmethod
+        def barrier(): pass
+        @staticmethod
+        def all_reduce(t, op=None): return t
+        @staticmethod
+        def destroy_process_group(): pass
+    if world == 1:
+        dist = _Solo
 
     host = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
     host_np = host.numpy().view(capi.PARTICLE)
@@ -235,6 +275,9 @@ def bench_main(args, world, rank, local):
     owned = torch.tensor([len(vel)], device="cuda", dtype=torch.int64)
     dist.all_reduce(owned)
     total = int(owned.item())
+    expect = torch.tensor([n_own], device="cuda", dtype=torch.int64)
+    dist.all_reduce(expect)
+    assert total == int(expect.item()), f"particles lost or duplicated by the exchange: {total} owned, {int(expect.item())} generated"
     value = total * args.steps / (ms * 1e-3)
 
     # end to end on host records: upload own records, exchange ghosts, step, download own records
@@ -267,7 +310,7 @@ def bench_main(args, world, rank, local):
             "metric": B.METRIC, "value": value, "unit": B.UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": B.WORKLOADS[args.workload] + f", one tank section per GPU ({world} sections side by side)",
+            "config": {"workload": B.WORKLOADS[args.workload] + what,
                        "particles": total, "particles_per_gpu": n_own, "decomposition": "x slabs, halo = 2 support radii, "
                        "one NCCL send/recv pair per neighbour per step", "l2": "state exceeds the 126 MB L2",
                        "accel_output": not args.no_accel},
