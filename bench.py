@@ -294,6 +294,19 @@ def main():
     e2e = {"value": n / t_e2e, "unit": UNIT, "h2d_bytes_per_step": n * 52, "d2h_bytes_per_step": n * 52,
            "ms_per_step": 1e3 * t_e2e, "call": "sphb_step_aos (52-byte Particle records, pinned host memory)"}
 
+    # ---- the viewer's loop (main.cpp idle -> step_scene -> update_positions): state resident, positions back every step
+    xyz = torch.empty(n * 3, dtype=torch.float32).pin_memory()
+    eng.upload_soa_device(init[0].data_ptr(), init[1].data_ptr(), n)
+    eng.step(1); eng.download_positions(ptr=xyz.data_ptr(), n=n)
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        eng.step(1)
+        eng.download_positions(ptr=xyz.data_ptr(), n=n)
+    t_view = (time.perf_counter() - t0) / e2e_steps
+    e2e["viewer_loop"] = {"value": n / t_view, "unit": UNIT, "ms_per_step": 1e3 * t_view, "h2d_bytes_per_step": 0,
+                          "d2h_bytes_per_step": n * 12, "call": "sphb_step + sphb_download_positions (state stays on the GPU, "
+                          "12 B/particle come back: what main.cpp's update_positions needs each frame)"}
+
     # ---- roofline of the dominant kernel
     peak, peak_src = measured_peak()
     bforce = B_FORCE_NOACC if args.no_accel else B_FORCE

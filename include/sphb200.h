@@ -128,6 +128,10 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
  * sphb_count: the first n particles of the original order are returned. */
 int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask);
 
+/* Positions only, packed x,y,z (12 B per particle), original order: what the viewer's update_positions() copies into
+ * its vertex buffer every frame (main.cpp:97-110).  A quarter of the PCIe traffic of a full-record download. */
+int sphb_download_positions(sphb_engine* e, float* xyz, size_t n);
+
 /* --- the five public methods of SphUtils (SPH/SphUtils.hpp:40-44), on the device-resident state ---- */
 
 /* update_cells (SphUtils.cpp:8-47): bounding box, cell coordinates, stable counting sort; the state is
@@ -198,6 +202,31 @@ int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, v
 int sphb_download_soa(sphb_engine* e, float* posm, float* vel, float* aux, float* accel, int32_t* ids);
 /* The CUDA stream (cudaStream_t) all of this engine's work is enqueued on. */
 void* sphb_stream(sphb_engine* e);
+
+/* --- headless point-sprite renderer (the arithmetic of SPH/Shaders/sph.vertexshader + sph.fragmentshader) ------ */
+/* The viewer draws every particle as a GL point sprite whose fragment shader turns it into a sphere impostor and
+ * writes its clip-space depth as a grey value (main.cpp:229-252, sph.vertexshader:8-12, sph.fragmentshader:7-24).
+ * No graphics API exists on the target machines; this is the same arithmetic as a CUDA kernel into a plain float
+ * image.  Per particle: clip = MVP (pos, 1); culled unless -w <= x,y,z <= w; window centre ((x/w + 1)/2 W,
+ * (y/w + 1)/2 H); sprite edge = point_scale / clip.w pixels, clamped to [1, 2048]; a pixel whose centre lies in the
+ * sprite square gets N.xy = 2 (s,t) - 1 with (s,t) = 1/2 + (pixel centre - window centre) / edge (origin lower
+ * left, main.cpp:565), is discarded if |N.xy|^2 > 1, else N.z = sqrt(1 - |N.xy|^2) and
+ * value = clamp((MVP (pos + sprite_radius N, 1)).z / .w, 0, 1).  No depth buffer is requested by the viewer
+ * (GLUT_DOUBLE | GLUT_RGB, main.cpp:730), so a later particle overwrites an earlier one: particle order decides. */
+typedef struct sphb_camera {
+    float mvp[16];        /* column-major, like glm::mat4 / glUniformMatrix4fv(..., GL_FALSE, ...) */
+    int32_t width, height;
+    float point_scale;    /* 50   (sph.vertexshader:10) */
+    float sprite_radius;  /* 0.1  (sph.fragmentshader:19) */
+    float clear_value;    /* 1.0  (glClearColor(1,1,1,1), main.cpp:230) */
+} sphb_camera;
+
+/* main.cpp:48-60: perspective(45.0f [radians in GLM 0.9.6], 4/3, 0.1, 100) * lookAt((0,-0.8,1.5), (0,-0.8,0),
+ * (0,1,0)) * identity; 1080 x 920 (main.cpp:13-14). */
+void sphb_default_camera(sphb_camera* cam);
+
+/* Renders the current particle positions (original order) into image[height][width] (row 0 = bottom, as GL). */
+int sphb_render_depth(sphb_engine* e, const sphb_camera* cam, float* image);
 
 /* --- multi-GPU: x-slab decomposition, one engine (one process) per GPU ------------------------------- */
 /* Nothing like this exists in the reference (single thread).  Each rank owns the particles

@@ -160,6 +160,18 @@ class Oracle:
         self.lib.orc_grid_build(C.byref(g), _vp(ps), C.c_size_t(n), _vp(xyz), _vp(key), _vp(perm), _vp(start))
         return xyz, key, perm, start
 
+    # --- viewer picture (shader arithmetic restated; parity unpinned: no graphics API on this box)
+    def default_mvp(self) -> np.ndarray:
+        m = np.zeros(16, np.float32)
+        self.lib.orc_default_mvp(_vp(m))
+        return m
+
+    def render_depth(self, ps, mvp, width=1080, height=920, point_scale=50.0, sprite_radius=0.1, clear_value=1.0):
+        img = np.zeros((height, width), np.float32)
+        self.lib.orc_render_depth(_vp(np.ascontiguousarray(ps)), C.c_size_t(len(ps)), _f3(mvp), C.c_int(width), C.c_int(height),
+                                  C.c_float(point_scale), C.c_float(sprite_radius), C.c_float(clear_value), _vp(img))
+        return img
+
     # --- scene (main.cpp:424-540)
     def scene_default(self):
         ps = np.zeros(1300, PARTICLE)

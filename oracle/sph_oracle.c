@@ -603,3 +603,80 @@ uint64_t orc_fnv1a_pos(const orc_particle* ps, size_t n) {
         }
     return hsh;
 }
+
+/* ---- viewer picture: the shader arithmetic restated on the CPU (parity UNPINNED for this part) -------------
+ * SPH/Shaders/sph.vertexshader:8-12, sph.fragmentshader:7-24, main.cpp:48-60,229-252,563-571.  Running the GLSL
+ * itself needs a graphics API, which is unavailable on this box, so nothing here can be checked against the
+ * reference's own output; it is the checker for the CUDA splat kernel only. */
+
+/* main.cpp:48-60 with GLM 0.9.6.1 gtc/matrix_transform.inl:212-232 (perspective, fovy in radians) and :388-413 (lookAt) */
+void orc_default_mvp(float mvp[16]) {
+    float fovy = 45.0f, aspect = 4.0f / 3.0f, zn = 0.1f, zf = 100.0f;
+    float th = tanf(fovy / 2.0f);
+    float P[4][4], V[4][4];
+    memset(P, 0, sizeof P);
+    memset(V, 0, sizeof V);
+    P[0][0] = 1.0f / (aspect * th);
+    P[1][1] = 1.0f / th;
+    P[2][2] = -(zf + zn) / (zf - zn);
+    P[2][3] = -1.0f;
+    P[3][2] = -(2.0f * zf * zn) / (zf - zn);
+    float eye[3] = {0.0f, -0.8f, 1.5f}, center[3] = {0.0f, -0.8f, 0.0f}, up[3] = {0.0f, 1.0f, 0.0f};
+    float d[3], f[3], s0[3], s[3], u[3];
+    g_sub(center, eye, d);
+    g_normalize(d, f);
+    s0[0] = f[1] * up[2] - up[1] * f[2]; s0[1] = f[2] * up[0] - up[2] * f[0]; s0[2] = f[0] * up[1] - up[0] * f[1];
+    g_normalize(s0, s);
+    u[0] = s[1] * f[2] - f[1] * s[2]; u[1] = s[2] * f[0] - f[2] * s[0]; u[2] = s[0] * f[1] - f[0] * s[1];
+    for (int a = 0; a < 4; a++) V[a][a] = 1.0f;
+    V[0][0] = s[0]; V[1][0] = s[1]; V[2][0] = s[2];
+    V[0][1] = u[0]; V[1][1] = u[1]; V[2][1] = u[2];
+    V[0][2] = -f[0]; V[1][2] = -f[1]; V[2][2] = -f[2];
+    V[3][0] = -g_dot(s, eye); V[3][1] = -g_dot(u, eye); V[3][2] = g_dot(f, eye);
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 4; r++) {
+            float acc = 0.0f;
+            for (int k = 0; k < 4; k++) acc += P[k][r] * V[c][k];
+            mvp[4 * c + r] = acc;
+        }
+}
+
+static void mvp_apply(const float m[16], float x, float y, float z, float out[4]) {
+    for (int r = 0; r < 4; r++) out[r] = m[r] * x + m[4 + r] * y + m[8 + r] * z + m[12 + r];
+}
+
+/* particles in order, later ones overwrite (no depth buffer, main.cpp:730); image[h][w], row 0 at the bottom */
+void orc_render_depth(const orc_particle* ps, size_t n, const float mvp[16], int width, int height, float point_scale,
+                      float sprite_radius, float clear_value, float* image) {
+    for (long i = 0; i < (long)width * height; i++) image[i] = clear_value;
+    for (size_t k = 0; k < n; k++) {
+        float clip[4];
+        mvp_apply(mvp, ps[k].pos[0], ps[k].pos[1], ps[k].pos[2], clip);
+        if (!(clip[3] > 0.0f) || fabsf(clip[0]) > clip[3] || fabsf(clip[1]) > clip[3] || fabsf(clip[2]) > clip[3]) continue;
+        float xw = (clip[0] / clip[3] * 0.5f + 0.5f) * (float)width, yw = (clip[1] / clip[3] * 0.5f + 0.5f) * (float)height;
+        float edge = point_scale / clip[3];
+        if (edge < 1.0f) edge = 1.0f;
+        if (edge > 2048.0f) edge = 2048.0f;
+        int x0 = (int)floorf(xw - 0.5f * edge), x1 = (int)ceilf(xw + 0.5f * edge);
+        int y0 = (int)floorf(yw - 0.5f * edge), y1 = (int)ceilf(yw + 0.5f * edge);
+        if (x0 < 0) x0 = 0;
+        if (y0 < 0) y0 = 0;
+        if (x1 > width - 1) x1 = width - 1;
+        if (y1 > height - 1) y1 = height - 1;
+        for (int py = y0; py <= y1; py++)
+            for (int px = x0; px <= x1; px++) {
+                float s = 0.5f + ((float)px + 0.5f - xw) / edge, t = 0.5f + ((float)py + 0.5f - yw) / edge;
+                if (s < 0.0f || s >= 1.0f || t < 0.0f || t >= 1.0f) continue;
+                float nx = s * 2.0f - 1.0f, ny = t * 2.0f - 1.0f;
+                float mag = nx * nx + ny * ny;
+                if (mag > 1.0f) continue;
+                float nz = sqrtf(1.0f - mag);
+                float cp[4];
+                mvp_apply(mvp, ps[k].pos[0] + nx * sprite_radius, ps[k].pos[1] + ny * sprite_radius, ps[k].pos[2] + nz * sprite_radius, cp);
+                float depth = cp[2] / cp[3];
+                if (depth < 0.0f) depth = 0.0f;
+                if (depth > 1.0f) depth = 1.0f;
+                image[(size_t)py * width + px] = depth;
+            }
+    }
+}

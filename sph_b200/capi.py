@@ -32,6 +32,13 @@ class SphbError(RuntimeError):
     pass
 
 
+class Camera(C.Structure):
+    """struct sphb_camera (include/sphb200.h)."""
+
+    _fields_ = [("mvp", C.c_float * 16), ("width", C.c_int32), ("height", C.c_int32), ("point_scale", C.c_float),
+                ("sprite_radius", C.c_float), ("clear_value", C.c_float)]
+
+
 class Slab(C.Structure):
     """struct sphb_slab (include/sphb200.h)."""
 
@@ -62,7 +69,7 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_count_nonfinite", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
+    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
 ]
 
 _lib = None
@@ -95,6 +102,10 @@ def load_library() -> C.CDLL:
     L.sphb_get_spheres.argtypes = [vp, vp, sz, sz]
     L.sphb_upload_aos.argtypes = [vp, vp, sz, sz]
     L.sphb_download_aos.argtypes = [vp, vp, sz, sz, u32]
+    L.sphb_download_positions.argtypes = [vp, vp, sz]
+    L.sphb_default_camera.argtypes = [C.POINTER(Camera)]
+    L.sphb_default_camera.restype = None
+    L.sphb_render_depth.argtypes = [vp, C.POINTER(Camera), vp]
     for name in ("sphb_update_cells", "sphb_update_density", "sphb_update_forces", "sphb_update_posvel",
                  "sphb_collision", "sphb_synchronize"):
         getattr(L, name).argtypes = [vp]
@@ -139,6 +150,12 @@ def default_params(**overrides) -> Params:
         else:
             setattr(p, k, v)
     return p
+
+
+def default_camera() -> Camera:
+    cam = Camera()
+    load_library().sphb_default_camera(C.byref(cam))
+    return cam
 
 
 def _ptr(a):
@@ -210,6 +227,23 @@ class Engine:
         assert particles.dtype == PARTICLE and particles.flags.c_contiguous
         self._check(self.lib.sphb_download_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize, mask))
         return particles
+
+    def render_depth(self, camera: "Camera | None" = None) -> np.ndarray:
+        """The viewer's picture of the current state as a float image [height, width], row 0 at the bottom."""
+        cam = camera if camera is not None else default_camera()
+        img = np.zeros((cam.height, cam.width), np.float32)
+        self._check(self.lib.sphb_render_depth(self.h, C.byref(cam), _ptr(img)))
+        return img
+
+    def download_positions(self, xyz: np.ndarray | None = None, ptr: int | None = None, n: int | None = None):
+        """Packed x,y,z in original order into `xyz` (float32 [n,3]) or a raw host pointer."""
+        if ptr is not None:
+            self._check(self.lib.sphb_download_positions(self.h, C.c_void_p(ptr), n))
+            return None
+        if xyz is None:
+            xyz = np.zeros((self.count(), 3), np.float32)
+        self._check(self.lib.sphb_download_positions(self.h, _ptr(xyz), len(xyz)))
+        return xyz
 
     def download_first(self, particles: np.ndarray, mask: int = F_ALL):
         """Download the first len(particles) particles of the original order (the rest may be ghosts)."""

@@ -489,6 +489,89 @@ int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, 
     return SPHB_OK;
 }
 
+int sphb_download_positions(sphb_engine* e, float* xyz, size_t n) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (n > e->n) return fail(SPHB_ERR_INVALID, "download of %zu particles but the engine holds %zu", n, e->n);
+    if (n && !xyz) return fail(SPHB_ERR_INVALID, "null output");
+    if (n == 0) return SPHB_OK;
+    const int cur = e->cur;
+    CK(e->scratch.reserve(3 * n));
+    LAUNCH(e, k_invert_perm, cdiv(e->n, 256), 256, 0, e->oid[cur].p, e->inv.p, (int)e->n);
+    LAUNCH(e, k_positions_packed, cdiv(n, 256), 256, 0, e->posm[cur].p, e->inv.p, e->scratch.p, (int)n);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(xyz, e->scratch.p, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return SPHB_OK;
+}
+
+void sphb_default_camera(sphb_camera* cam) {
+    if (!cam) return;
+    memset(cam, 0, sizeof *cam);
+    // glm::perspective(45.0f, 4.0f/3.0f, 0.1f, 100.0f): fovy is in RADIANS in GLM 0.9.6 (gtc/matrix_transform.inl:212-232)
+    const float fovy = 45.0f, aspect = 4.0f / 3.0f, zn = 0.1f, zf = 100.0f;
+    const float th = tanf(fovy / 2.0f);
+    float P[16] = {0}, V[16] = {0};
+    P[0] = 1.0f / (aspect * th);
+    P[5] = 1.0f / th;
+    P[10] = -(zf + zn) / (zf - zn);
+    P[11] = -1.0f;
+    P[14] = -(2.0f * zf * zn) / (zf - zn);
+    // glm::lookAt(eye (0,-0.8,1.5), center (0,-0.8,0), up (0,1,0))  (gtc/matrix_transform.inl:388-413)
+    const float eye[3] = {0.0f, -0.8f, 1.5f}, ctr[3] = {0.0f, -0.8f, 0.0f}, up[3] = {0.0f, 1.0f, 0.0f};
+    float f[3] = {ctr[0] - eye[0], ctr[1] - eye[1], ctr[2] - eye[2]};
+    float fl = 1.0f / sqrtf(f[0] * f[0] + f[1] * f[1] + f[2] * f[2]);
+    for (int a = 0; a < 3; a++) f[a] *= fl;
+    float sv[3] = {f[1] * up[2] - f[2] * up[1], f[2] * up[0] - f[0] * up[2], f[0] * up[1] - f[1] * up[0]};
+    float sl = 1.0f / sqrtf(sv[0] * sv[0] + sv[1] * sv[1] + sv[2] * sv[2]);
+    for (int a = 0; a < 3; a++) sv[a] *= sl;
+    const float u[3] = {sv[1] * f[2] - sv[2] * f[1], sv[2] * f[0] - sv[0] * f[2], sv[0] * f[1] - sv[1] * f[0]};
+    V[0] = sv[0]; V[4] = sv[1]; V[8] = sv[2];
+    V[1] = u[0];  V[5] = u[1];  V[9] = u[2];
+    V[2] = -f[0]; V[6] = -f[1]; V[10] = -f[2];
+    V[12] = -(sv[0] * eye[0] + sv[1] * eye[1] + sv[2] * eye[2]);
+    V[13] = -(u[0] * eye[0] + u[1] * eye[1] + u[2] * eye[2]);
+    V[14] = f[0] * eye[0] + f[1] * eye[1] + f[2] * eye[2];
+    V[15] = 1.0f;
+    for (int col = 0; col < 4; col++)       // MVP = P * V * I, column-major
+        for (int row = 0; row < 4; row++) {
+            float acc = 0.0f;
+            for (int k = 0; k < 4; k++) acc += P[k * 4 + row] * V[col * 4 + k];
+            cam->mvp[col * 4 + row] = acc;
+        }
+    cam->width = 1080;   // main.cpp:13-14
+    cam->height = 920;
+    cam->point_scale = 50.0f;
+    cam->sprite_radius = 0.1f;
+    cam->clear_value = 1.0f;
+}
+
+int sphb_render_depth(sphb_engine* e, const sphb_camera* cam, float* image) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (!cam || !image) return fail(SPHB_ERR_INVALID, "null argument");
+    if (cam->width <= 0 || cam->height <= 0 || (long long)cam->width * cam->height > (1ll << 28)) return fail(SPHB_ERR_INVALID, "bad image size");
+    Camera c;
+    memcpy(c.m, cam->mvp, sizeof c.m);
+    c.width = cam->width; c.height = cam->height;
+    c.point_scale = cam->point_scale; c.sprite_radius = cam->sprite_radius; c.clear_value = cam->clear_value;
+    const size_t npix = (size_t)c.width * c.height;
+    const int n = (int)e->n, cur = e->cur;
+    CK(e->scratch.reserve(2 * npix));
+    unsigned int* winner = (unsigned int*)e->scratch.p;
+    float* d_img = e->scratch.p + npix;
+    CK(cudaMemsetAsync(winner, 0, npix * sizeof(unsigned int), e->stream));
+    if (n) {
+        LAUNCH(e, k_invert_perm, cdiv(n, 256), 256, 0, e->oid[cur].p, e->inv.p, n);
+        LAUNCH(e, k_splat_winner, cdiv((long long)n * 32, 256), 256, 0, c, e->posm[cur].p, e->inv.p, n, winner);
+    }
+    LAUNCH(e, k_splat_shade, cdiv(npix, 256), 256, 0, c, e->posm[cur].p, e->inv.p, winner, d_img);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(image, d_img, npix * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return SPHB_OK;
+}
+
 int sphb_update_cells(sphb_engine* e) {
     int rc = check_ready(e);
     if (rc) return rc;
