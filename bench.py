@@ -198,6 +198,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-accel", action="store_true", help="skip the per-particle acceleration output (72 B force kernel)")
     ap.add_argument("--domain", default="fixed", choices=["fixed", "bbox"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="multi-GPU: weak = one 16.7 M-particle tank section per GPU (default); strong = the ONE config-4 tank "
+                         "cut into N slabs at particle-count quantiles")
     ap.add_argument("--reset-every", type=int, default=16,
                     help="restore the initial state (device-to-device, inside the timed region) every this many steps: the "
                          "reference's scheme (dt=0.033, k=100) blows up on deep pools after ~35 steps, in its own arithmetic too")

@@ -1,10 +1,12 @@
 // Headless driver: the reference's scene set-up and step loop (SPH/main.cpp initScene :555-559,
 // initParticles :490-505, addParticle :424-442, initWalls :508-540, step_scene :280-303) with every GL /
 // GLUT call left out, driving the engine through the drop-in SphUtils class exactly as main.cpp does.
-//   sph_headless [steps=20] [fused|methods] [emit]
+//   sph_headless [steps=20] [fused|methods] [emit|noemit] [picture.pgm]
 // "fused" uses SphUtils::step_scene (one sphb_step_aos call per step) instead of the four methods.
 // "emit" switches the emitter of step_scene on (main.cpp:281-290, the Enter key): one particle per step from
 // rand(), until MAX_PARTICLES -- the particle vector grows between steps and the engine follows.
+// A last argument ending in .pgm writes the viewer's picture of the final state (sphb_render_depth: the arithmetic
+// of the reference's point-sprite shaders as CUDA kernels; 1080 x 920, 8-bit grey, top row first).
 // Prints particle count and, per reported step, mean density, kinetic energy and the FNV-1a-64 hash of the
 // position bits (the same hash tests/golden/default_scene.npz holds for the compiled reference).
 #include <stdint.h>
@@ -103,6 +105,24 @@ int main(int argc, char** argv) {
             printf("step %d mean_rho %.6f ke %.6f fnv %016llx n %zu\n", s, rho / particles.size(), ke, (unsigned long long)fnv_pos(),
                    particles.size());
         }
+    }
+    const char* pgm = argc > 4 ? argv[4] : 0;
+    if (pgm) {
+        sphb_camera cam;
+        sphb_default_camera(&cam);
+        std::vector<float> img((size_t)cam.width * cam.height);
+        // the picture is taken from the engine's resident copy of the particles (it holds the state of the last call)
+        if (sphb_render_depth(sph.engine(), &cam, &img[0]) != SPHB_OK) {
+            fprintf(stderr, "render failed: %s\n", sphb_last_error());
+            return 3;
+        }
+        FILE* f = fopen(pgm, "wb");
+        if (!f) return 4;
+        fprintf(f, "P5\n%d %d\n255\n", cam.width, cam.height);
+        for (int y = cam.height - 1; y >= 0; y--)          // image rows are bottom-up (GL), PGM is top-down
+            for (int x = 0; x < cam.width; x++) fputc((int)(img[(size_t)y * cam.width + x] * 255.0f + 0.5f), f);
+        fclose(f);
+        printf("wrote %s\n", pgm);
     }
     return 0;
 }

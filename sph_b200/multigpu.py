@@ -192,11 +192,18 @@ def bench_main(args, world, rank, local):
         scale = {"drop16m": 1, "drop2m": 2, "drop256k": 4}.get(args.workload)
         if scale is None:
             raise SystemExit("multi-GPU bench runs the block-drop (drop16m / drop2m / drop256k) and periodic workloads")
-        section = 256 // scale * 0.1                     # x-length of one tank section = one GPU's share
-        ps = scenes.block_drop_section(rank, world, scale=scale)
-        walls = scenes.tank_walls(section * world + 0.2, section + 0.2)
+        section = 256 // scale * 0.1                     # x-length of one tank section
+        strong = getattr(args, "scaling", "weak") == "strong"
+        if strong:
+            # config 4 as written: ONE tank, N slabs whose boundaries sit at particle-count quantiles of x
+            ps, walls = scenes.block_drop(scale=scale)
+            bounds = quantile_bounds(ps["pos"][:, 0], world, R, 0.0, section + 0.2)
+            ps = ps[(ps["pos"][:, 0] >= (bounds[rank] if rank else -1e30)) & (ps["pos"][:, 0] < (bounds[rank + 1] if rank < world - 1 else 1e30))].copy()
+        else:
+            ps = scenes.block_drop_section(rank, world, scale=scale)
+            walls = scenes.tank_walls(section * world + 0.2, section + 0.2)
+            bounds = [0.1 + section * r for r in range(world + 1)]
         n_own = len(ps)
-        bounds = [0.1 + section * r for r in range(world + 1)]
         slab = make_slab(rank, world, bounds, halo)
         left, right = neighbours(rank, world)
         top = 0.1 + (192 + 256) // scale * 0.1 + 0.3 + 1.0
@@ -205,10 +212,12 @@ def bench_main(args, world, rank, local):
         eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi,
                           write_accel=0 if args.no_accel else 1)
         eng.set_walls(walls)
-        face = (section + 0.2) * (192 // scale * 0.1 + 0.5) * 1100.0      # particles per unit x near a face (upper bound)
+        column = (192 + (256 if strong else 0)) // scale * 0.1 + 0.5        # a strong-scaling cut may pass through the falling block
+        face = (section + 0.2) * column * 1100.0                             # particles per unit x near a face (upper bound)
         capacity = int(face * halo * 2.0) + 4096
         eng.reserve(n_own + 2 * capacity)
-        what = f", one tank section per GPU ({world} sections side by side)"
+        what = (f", ONE tank cut into {world} x-slabs at particle-count quantiles" if strong
+                else f", one tank section per GPU ({world} sections side by side)")
     sr = SlabRank(eng, slab, capacity, local)
 
     class _Solo:  # world size 1: no process group; the only "collectives" are identities
@@ -308,7 +317,7 @@ def bench_main(args, world, rank, local):
         ach = bforce * n_local / (float(phase[2]) * 1e-3) / 1e9
         line = {
             "metric": B.METRIC, "value": value, "unit": B.UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": getattr(args, "scaling", "weak"), "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": B.WORKLOADS[args.workload] + what,
                        "particles": total, "particles_per_gpu": n_own, "decomposition": "x slabs, halo = 2 support radii, "

@@ -588,3 +588,16 @@ def test_splat_renderer_matches_cpu_restatement(eng, oracle):
     differ = np.abs(got - want) > 1e-5
     assert differ.sum() <= 1e-3 * covered.sum(), f"{differ.sum()} of {covered.sum()} covered pixels differ"   # sprite-edge ties only
     assert np.array_equal(got == 1.0, want == 1.0) or differ.sum() <= 1e-3 * covered.sum()
+
+
+def test_headless_cpp_driver_writes_the_viewer_picture(tmp_path):
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "sph_b200", "host", "sph_headless")
+    out_file = tmp_path / "frame.pgm"
+    out = subprocess.run([exe, "15", "fused", "noemit", str(out_file)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    data = out_file.read_bytes()
+    assert data.startswith(b"P5\n1080 920\n255\n") and len(data) == len(b"P5\n1080 920\n255\n") + 1080 * 920
+    px = np.frombuffer(data[-1080 * 920:], np.uint8)
+    assert 0.05 < (px < 255).mean() < 0.9          # the fluid is in the picture, on a white ground
