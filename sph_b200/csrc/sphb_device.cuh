@@ -343,6 +343,11 @@ __global__ void __launch_bounds__(256) k_scatter(const int* __restrict__ key, co
     pairs[cell_start[key[i]] + slot[i]] = make_int2(oid[i], i);
 }
 
+// A cell that holds more than this many particles (a clamped boundary cell full of strays, or everything gone
+// NaN and filed under cell 0) keeps its ARRIVAL order instead: counting smaller ids is quadratic in the cell size.
+// Still a valid permutation, just not the stable one (and not reproducible run to run) for that cell.
+constexpr int kStableRankLimit = 4096;
+
 template <bool kCarryAll>
 __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pairs, const int* __restrict__ key, const int* __restrict__ cell_start,
                                                      const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
@@ -356,7 +361,11 @@ __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pa
     const int k = key[me.y];
     const int b = cell_start[k], e = cell_start[k + 1];
     int rank = 0;
-    for (int q = b; q < e; q++) rank += (pairs[q].x < me.x);
+    if (e - b <= kStableRankLimit) {
+        for (int q = b; q < e; q++) rank += (pairs[q].x < me.x);
+    } else {
+        rank = p - b; // arrival order
+    }
     const int dst = b + rank;
     posm_out[dst] = ldg4(posm_in + me.y);
     vel_out[dst] = ldg4(vel_in + me.y);
