@@ -26,9 +26,12 @@ def test_slab_tables():
     assert (p2.hi, p2.has_right, p2.shift_right) == (4.0, 1, -4.0)
     assert multigpu.neighbours(0, 3) == (None, 1) and multigpu.neighbours(2, 3) == (1, None)
     assert multigpu.neighbours(0, 3, periodic=True) == (2, 1) and multigpu.neighbours(2, 3, periodic=True) == (1, 0)
-    assert multigpu.neighbours(0, 1, periodic=True) == (None, None)
+    assert multigpu.neighbours(0, 1, periodic=True) == (0, 0)            # a lone rank in a periodic box is its own neighbour
     one = multigpu.make_slab(0, 1, [0.0, 4.0], 0.4)
     assert (one.lo, one.hi, one.has_left, one.has_right) == (-math.inf, math.inf, 0, 0)
+    solo = multigpu.make_slab(0, 1, [0.0, 4.0], 0.4, period=4.0, yz_box=((0.0, 2.0), None))
+    assert (solo.lo, solo.hi, solo.has_left, solo.has_right, solo.shift_left, solo.shift_right) == (0.0, 4.0, 1, 1, 4.0, -4.0)
+    assert (solo.periodic_y, solo.ylo, solo.ylen, solo.periodic_z) == (1, 0.0, 2.0, 0)
 
 
 def test_quantile_bounds_balance():
