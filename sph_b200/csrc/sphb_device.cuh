@@ -1295,21 +1295,54 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_count(Slab s, const float4* _
     }
 }
 
-// pass 2: one block turns the per-block counts into exclusive offsets (3 interleaved streams) and totals
-__global__ void __launch_bounds__(kMgThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int* __restrict__ totals) {
-    int carry[3] = {0, 0, 0};
-    for (int base = 0; base < nblocks; base += kMgThreads) {
-        const int b = base + threadIdx.x;
+// pass 2: the per-block counts become exclusive offsets (and totals).  One block of 1024 threads per stream
+// (keep / left / right), four entries per thread per round: 70 K blocks take 18 rounds (the first version, one
+// 256-thread block for all three streams, took 0.34 ms of a 7.4 ms step at 17.8 M particles).
+constexpr int kMgScanThreads = 1024;
+
+__global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int* __restrict__ totals) {
+    __shared__ int s_warp[kMgScanThreads / 32];
+    const int k = blockIdx.x; // stream
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int carry = 0;
+    for (int base = 0; base < nblocks; base += 4 * kMgScanThreads) {
+        const int b0 = base + 4 * threadIdx.x;
+        int v[4];
+        int tsum = 0;
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            const int v = b < nblocks ? block_counts[3 * b + k] : 0;
-            int tot;
-            const int ex = block_exclusive_scan(v, &tot);
-            if (b < nblocks) block_counts[3 * b + k] = carry[k] + ex;
-            carry[k] += tot;
+        for (int q = 0; q < 4; q++) {
+            v[q] = (b0 + q < nblocks) ? block_counts[3 * (b0 + q) + k] : 0;
+            tsum += v[q];
         }
+        int inc = tsum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w; // inclusive over warps
+        }
+        __syncthreads();
+        int ex = carry + (warp ? s_warp[warp - 1] : 0) + inc - tsum;
+        const int round_total = s_warp[kMgScanThreads / 32 - 1];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (b0 + q < nblocks) block_counts[3 * (b0 + q) + k] = ex;
+            ex += v[q];
+        }
+        carry += round_total;
+        __syncthreads(); // s_warp is reused next round
     }
-    if (threadIdx.x < 3) totals[threadIdx.x] = carry[threadIdx.x];
+    if (threadIdx.x == 0) totals[k] = carry;
 }
 
 // pass 3: write.  keep -> (posm_out, vel_out) with the ownership flag refreshed; left/right -> messages.

@@ -906,7 +906,7 @@ extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_lef
     e->mg_blocks = nb;
     int* totals = e->mg_counts.p + 3 * nb;
     LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p);
-    LAUNCH(e, k_mg_scan, 1, kMgThreads, 0, e->mg_counts.p, nb, totals);
+    LAUNCH(e, k_mg_scan, 3, kMgScanThreads, 0, e->mg_counts.p, nb, totals);
     const int out_cap = (int)(e->posm[nxt].cap < 0x7fffffffu ? e->posm[nxt].cap : 0x7fffffffu);
     LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, e->posm[nxt].p,
            e->vel[nxt].p, out_cap, (float4*)msg_left, (float4*)msg_right, (int)capacity);
