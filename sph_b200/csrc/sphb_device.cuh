@@ -776,8 +776,9 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
                                                const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
                                                float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                BBoxAcc* bbox, int n) {
-    __shared__ unsigned int s_mask[2 * kRows][128];
-    __shared__ int s_jb[kRows][128];
+    __shared__ unsigned int s_word[2 * kRows][128];  // this thread's NON-EMPTY mask words, compacted ...
+    __shared__ unsigned char s_idx[2 * kRows][128];  // ... which word each is (2*row + half) ...
+    __shared__ int s_jb[kRows][128];                 // ... and where each row's run starts
     const int tid = threadIdx.x;
     const int i = blockIdx.x * blockDim.x + tid;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -789,25 +790,29 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         int cx, cy, cz;
         cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
         bool crowded = false;
+        int nw = 0;
 #pragma unroll
         for (int r = 0; r < kRows; r++) {
             int jb, je;
             row_run(g, cell_start, cx, cy, cz, r, jb, je);
+            const unsigned int m0 = mask[(size_t)(2 * r) * n + i], m1 = mask[(size_t)(2 * r + 1) * n + i];
             s_jb[r][tid] = jb;
-            s_mask[2 * r][tid] = mask[(size_t)(2 * r) * n + i];
-            s_mask[2 * r + 1][tid] = mask[(size_t)(2 * r + 1) * n + i];
+            if (m0) { s_word[nw][tid] = m0; s_idx[nw][tid] = (unsigned char)(2 * r); nw++; }
+            if (m1) { s_word[nw][tid] = m1; s_idx[nw][tid] = (unsigned char)(2 * r + 1); nw++; }
             crowded |= (je - jb) > kMaskBits;
         }
         float ax = 0.0f, ay = 0.0f, az = 0.0f;
-        int w = -1, jb = 0; // w: current mask word (row w/2, half w&1)
+        // One neighbour per lane per iteration: a lane whose word ran dry steps to its next (non-empty) word first,
+        // so the lanes of a warp stay in lockstep on the pair body until their lists end.
+        int k = -1, jb = 0;
         unsigned int m = 0;
         for (;;) {
-            while (m == 0 && w < 2 * kRows - 1) {
-                ++w;
-                m = s_mask[w][tid];
+            if (m == 0) {
+                if (++k >= nw) break;
+                m = s_word[k][tid];
+                const int w = s_idx[k][tid];
                 jb = s_jb[w >> 1][tid] + ((w & 1) << 5);
             }
-            if (m == 0) break;
             const int j = jb + __ffs((int)m) - 1;
             m &= m - 1;
             const float4 pj = ldg4(posm + j);
