@@ -1012,7 +1012,7 @@ __global__ void __launch_bounds__(256) k_positions_packed(const float4* __restri
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o >= n) return;
     const float4 q = posm[inv[o]];
-    xyz[3 * o] = q.x; xyz[3 * o + 1] = q.y; xyz[3 * o + 2] = q.z;
+    xyz[(size_t)3 * o] = q.x; xyz[(size_t)3 * o + 1] = q.y; xyz[(size_t)3 * o + 2] = q.z;
 }
 
 // grid diagnostics for the bit-exact grid test: cell coordinates in ORIGINAL order
@@ -1025,7 +1025,7 @@ __global__ void __launch_bounds__(256) k_cells_xyz(const GridDesc* __restrict__ 
     int cx, cy, cz;
     cell_key(g, q.x, q.y, q.z, cx, cy, cz);
     const int o = oid[p];
-    xyz[3 * o] = cx; xyz[3 * o + 1] = cy; xyz[3 * o + 2] = cz;
+    xyz[(size_t)3 * o] = cx; xyz[(size_t)3 * o + 1] = cy; xyz[(size_t)3 * o + 2] = cz;
 }
 
 // ---------------------------------------------------------------------------------------------------

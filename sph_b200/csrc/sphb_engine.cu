@@ -432,6 +432,7 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->mg_pending = false;
     e->aos_valid = true;
     return SPHB_OK;
 }
@@ -460,6 +461,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->mg_pending = false;
     e->aos_valid = false;
     return SPHB_OK;
 }
