@@ -601,3 +601,35 @@ def test_headless_cpp_driver_writes_the_viewer_picture(tmp_path):
     assert data.startswith(b"P5\n1080 920\n255\n") and len(data) == len(b"P5\n1080 920\n255\n") + 1080 * 920
     px = np.frombuffer(data[-1080 * 920:], np.uint8)
     assert 0.05 < (px < 255).mean() < 0.9          # the fluid is in the picture, on a white ground
+
+
+# --------------------------------------------------------------------------------------------------
+# error behaviour of the C ABI (the reference has none: void methods, undefined behaviour on empty vectors)
+
+def test_api_errors_are_reported_not_fatal():
+    import ctypes as C
+    lib = sph_b200.load_library()
+    with sph_b200.Engine() as e:
+        with pytest.raises(sph_b200.SphbError, match="no particles uploaded"):
+            e.step(1)
+        ps, walls = scenes.default_scene()
+        assert lib.sphb_upload_aos(e.h, ps.ctypes.data_as(C.c_void_p), len(ps), 50) == 1          # stride not a multiple of 4
+        assert b"stride" in lib.sphb_last_error()
+        e.upload(ps)
+        with pytest.raises(sph_b200.SphbError, match="no grid"):
+            e.get_cells()
+        big = np.zeros(len(ps) + 1, sph_b200.PARTICLE)
+        with pytest.raises(sph_b200.SphbError, match="download of"):
+            e.download(big)
+        too_many = np.zeros(17, sph_b200.WALL)
+        with pytest.raises(sph_b200.SphbError, match="at most 16 walls"):
+            e.set_walls(too_many)
+        e.set_walls(walls)
+        e.step(1)                                                                                 # still usable afterwards
+        assert e.count_nonfinite() == 0
+    for bad in (dict(h=0.0), dict(rho0=-1.0), dict(cell_size=0.01), dict(domain_mode=7), dict(periodic=(1, 0, 0)),
+                dict(domain_mode=1, domain_lo=(1, 0, 0), domain_hi=(0, 1, 1)), dict(cell_x_div=100)):
+        with pytest.raises(sph_b200.SphbError):
+            sph_b200.Engine(**bad)
+    with pytest.raises(sph_b200.SphbError, match="out of range"):
+        sph_b200.Engine(device=99)
