@@ -1,0 +1,104 @@
+// Shared device structures and helpers: grid descriptor, bounding-box accumulator, kernel constants, fast MUFU wrappers, cell coordinates.
+// Part of libsphb200.so (sm_100a); included through sphb_device.cuh.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sphb {
+
+
+constexpr int kMaxWalls = 16;
+constexpr int kMaxRows = 1 << 22; // cap on dims[1]*dims[2] ((y,z) rows of cells): bounds the row-group table
+
+// Device-resident description of the uniform grid (rebuilt every step by k_grid_setup).
+struct GridDesc {
+    float origin[3];
+    float cell[3]; // per axis (equal unless an axis is periodic and the cell was stretched to tile it)
+    int dims[3];
+    int ncell;     // dims[0]*dims[1]*dims[2]
+    int stencil;   // half width of the stencil in y and z cells: ceil(R / cell) (1 when cell >= R)
+    int stencil_x; // half width in x cells: ceil(R / cell_x)
+};
+
+// Bounding-box accumulator: floats mapped to order-preserving unsigned ints so atomicMin/Max work.
+struct BBoxAcc {
+    unsigned int lo[3];
+    unsigned int hi[3];
+};
+
+// Everything the physics kernels need, passed by value (lives in the kernel parameter space).
+struct Consts {
+    float h, h2, inv_h, inv_h2; // h2 = h*h (the support radius R), inv_h2 = 1/(h*h)
+    float R2;                   // R*R: a pair interacts iff d2 < R2
+    float Kw;                   // 315 / (64 pi h^9)
+    float Kg;                   // -45 / (pi h^6)
+    float Kl;                   // 45 / (pi h^6)
+    float rho0, eos_k, dt;
+    float gx, gy, gz;
+    float alpha, beta, eta_h2;  // eta_h2 = eta*h*h
+    float one_plus_e;           // 1 + restitution
+    double wall_off, wall_lim;
+    int nwalls;
+    float wn[kMaxWalls][3];     // wall normal (as given)
+    float wc[kMaxWalls][3];     // wall centre
+    float wu[kMaxWalls][3];     // normalize(normal), computed on the host with IEEE float ops
+    int domain_fixed;
+    float dom_lo[3], dom_hi[3];
+    int periodic[3];
+    long long max_cells;
+    float lap_coef; // coefficient of the optional Laplacian viscosity (SphUtils.cpp:277), 0 when off
+    float cell;   // cell edge in y and z
+    float cell_x; // cell edge in x (cell / cell_x_div)
+    int stencil_x;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// small helpers
+
+__device__ __forceinline__ unsigned int f2ord(float f) {
+    unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned int u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// MUFU approximations without the denormal fix-up code the C library versions carry (the pair body runs
+// ~40 times per particle per step; magnitudes here are nowhere near 1e-38).  <= 2 ulp each.
+__device__ __forceinline__ float fast_rsqrt(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_sqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// aux record (rho, P, sqrt|P/rho|, 1/rho).  The last two are helpers of the pair body (SphUtils.cpp:223,228),
+// never returned to the host; they are computed by this ONE function wherever they are needed (density
+// kernel, upload, per-neighbour re-derivation) so that every path sees the same bits.
+__device__ __forceinline__ float4 make_aux(float rho, float P) {
+    const float inv = fast_rcp(rho);
+    return make_float4(rho, P, fast_sqrt(fabsf(P * inv)), inv);
+}
+
+// Cell coordinate along one axis.  Same expression as SphUtils.cpp:38-40, floor((p - min) / cell), in
+// IEEE float (no FMA, true division), then clamped to the grid so that strays stay adjacent to their
+// neighbours.  Bit-exact against the CPU grid build the tests use.
+__device__ __forceinline__ int grid_coord(float x, float origin, float cell, int dim) {
+    float f = floorf(__fdiv_rn(__fsub_rn(x, origin), cell));
+    if (!(f >= 0.0f)) return 0;
+    if (f >= (float)dim) return dim - 1;
+    return (int)f;
+}
+
+} // namespace sphb

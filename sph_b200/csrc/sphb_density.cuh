@@ -1,0 +1,373 @@
+// Density + equation of state (SPH/SphUtils.cpp:55-63, 100-149): kernel shape, candidate runs, row groups, the packed-FP32 density kernel that also records the neighbour masks.
+// Part of libsphb200.so (sm_100a); included through sphb_device.cuh.
+#pragma once
+#include "sphb_common.cuh"
+#include "sphb_grid.cuh"
+
+namespace sphb {
+
+// ---------------------------------------------------------------------------------------------------
+// K3: scatter (original id, current index) pairs into their cell segment in arrival order, then
+// k_rank_gather replaces the arrival order by the STABLE order (ascending original id inside a cell,
+// i.e. exactly what a CPU stable counting sort of the uploaded order produces) and moves the state.
+
+__global__ void __launch_bounds__(256) k_scatter(const int* __restrict__ key, const int* __restrict__ slot, const int* __restrict__ oid,
+                                                 const int* __restrict__ cell_start, int2* __restrict__ pairs, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    pairs[cell_start[key[i]] + slot[i]] = make_int2(oid[i], i);
+}
+
+// A cell that holds more than this many particles (a clamped boundary cell full of strays, or everything gone
+// NaN and filed under cell 0) keeps its ARRIVAL order instead: counting smaller ids is quadratic in the cell size.
+// Still a valid permutation, just not the stable one (and not reproducible run to run) for that cell.
+constexpr int kStableRankLimit = 4096;
+
+template <bool kCarryAll>
+__global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pairs, const int* __restrict__ key, const int* __restrict__ cell_start,
+                                                     const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
+                                                     const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
+                                                     float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                     float4* __restrict__ aux_out, float4* __restrict__ acc_out,
+                                                     int* __restrict__ oid_out, int n) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int2 me = pairs[p];
+    const int k = key[me.y];
+    const int b = cell_start[k], e = cell_start[k + 1];
+    int rank = 0;
+    if (e - b <= kStableRankLimit) {
+        for (int q = b; q < e; q++) rank += (pairs[q].x < me.x);
+    } else {
+        rank = p - b; // arrival order
+    }
+    const int dst = b + rank;
+    posm_out[dst] = ldg4(posm_in + me.y);
+    vel_out[dst] = ldg4(vel_in + me.y);
+    if (kCarryAll) {
+        aux_out[dst] = ldg4(aux_in + me.y);
+        acc_out[dst] = ldg4(acc_in + me.y);
+    }
+    oid_out[dst] = me.x;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// SPH kernel shapes (SphUtils.cpp:55-95).  The reference evaluates the polynomial in double and rounds
+// once; here everything is FP32 with the constant factor applied after the neighbour sum
+// (tolerance-checked: <= 1e-5 relative on density and acceleration, tests/test_gpu_parity.py).
+
+// (h^2 - q^2)^3 with q^2 = d2/h^2, zero outside the support (q <= h  <=>  d2 <= h^4)
+__device__ __forceinline__ float w_shape(const Consts& c, float d2) {
+    float t = fmaxf(fmaf(-d2, c.inv_h2, c.h2), 0.0f);
+    return t * t * t;
+}
+
+// Candidate runs.  Around cell (cx,cy,cz) there are (2S+1)^2 rows (dz, dy); along x the 2Sx+1 cells of a
+// row are contiguous in the sorted arrays, so each row is ONE run [jb, je) of sorted slots.  Cells are
+// shorter in x than in y,z (cell_x = cell / cell_x_div): the run then spans 2R + 2 cell_x instead of 3R,
+// i.e. ~30 % fewer candidates to test for free (same number of runs, same two table look-ups per run).  Rows are
+// numbered canonically r = (dz+S)*(2S+1) + (dy+S) so that the density and force kernels agree on them;
+// a row outside the grid is the empty run.
+__device__ __forceinline__ void row_run(const GridDesc& g, const int* __restrict__ cell_start, int cx, int cy, int cz, int r,
+                                        int& jb, int& je) {
+    const int S = g.stencil, W = 2 * S + 1, Sx = g.stencil_x;
+    const int z = cz + r / W - S, y = cy + r % W - S;
+    jb = je = 0;
+    if (z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]) return;
+    const int x0 = max(cx - Sx, 0), x1 = min(cx + Sx, g.dims[0] - 1);
+    const int row = g.dims[0] * (y + g.dims[1] * z);
+    jb = __ldg(cell_start + row + x0);
+    je = __ldg(cell_start + row + x1 + 1);
+}
+
+// Neighbour masks.  While the density kernel tests every candidate of a run against the support radius
+// anyway, it records the outcome as one bit per candidate, two 32-bit words per row:
+// mask[(2r+w)*n + i] bit k  <=>  sorted slot jb_r + 32w + k is a neighbour of i (d2 < R^2, self excluded).  The force kernel then visits neighbours only --
+// no distance test on the ~85 % of candidates that fail it -- and its lanes stay converged on the heavy
+// pair body.  Candidates beyond the 64th of a run (crowded cells) are re-tested by the force kernel.
+constexpr int kMaskBits = 64;
+
+// ---------------------------------------------------------------------------------------------------
+// K4: density + equation of state (SphUtils.cpp:100-149) + neighbour masks.  One thread per sorted
+// particle.  aux = (rho, P, sqrt|P/rho|, 1/rho) (SphUtils.cpp:223 evaluates sqrt|P/rho| per pair).
+
+__device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
+    float rho = sum * c.Kw;
+    if (rho < c.rho0) rho = c.rho0;                 // SphUtils.cpp:141-142 (clamp UP)
+    float P = __fmul_rn(c.eos_k, __fsub_rn(rho, c.rho0)); // :144
+    return make_aux(rho, P);
+}
+
+// Row groups.  The density kernel gives each thread kDT consecutive sorted particles of ONE (y,z) row of cells,
+// so that they always share their candidate runs.  Row rho holds the slots [cell_start[rho*nx],
+// cell_start[(rho+1)*nx]) and is cut into ceil(len / kDT) groups; gstart = exclusive scan of the group counts
+// (nrows + 1 entries), one block.  Thread t of the density kernel finds its row by binary search in gstart.
+constexpr int kDT = 4;
+constexpr int kRgThreads = 1024;
+
+__global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                          int* __restrict__ gstart) {
+    __shared__ int s_warp[kRgThreads / 32];
+    __shared__ int s_carry;
+    const int nx = gd->dims[0], nrows = gd->dims[1] * gd->dims[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nrows; base += kRgThreads) {
+        const int rho = base + threadIdx.x;
+        int v = 0;
+        if (rho < nrows) v = (cell_start[(rho + 1) * nx] - cell_start[rho * nx] + kDT - 1) / kDT;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const int carry = s_carry;
+        const int ex = carry + (warp ? s_warp[warp - 1] : 0) + inc - v;
+        if (rho < nrows) gstart[rho] = ex;
+        __syncthreads();
+        if (threadIdx.x == kRgThreads - 1) s_carry = ex + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) gstart[nrows] = s_carry;
+}
+
+// The row rho with gstart[rho] <= t < gstart[rho + 1] (t = density-group index).  One 32-ary search per WARP
+// for its first thread (three dependent loads for 32 K rows instead of fifteen), then each lane walks on from
+// there: a warp covers ~128 particles, i.e. almost always one or two rows.  All 32 lanes must call it.
+__device__ __forceinline__ int find_row(const int* __restrict__ gstart, int nrows_grid, int t) {
+    const int lane = threadIdx.x & 31;
+    const int t0 = __shfl_sync(0xffffffffu, t, 0);
+    int lo = 0, hi = nrows_grid; // invariant: gstart[lo] <= t0 < gstart[hi]
+    while (hi - lo > 1) {
+        const int step = (hi - lo + 31) >> 5;
+        const int probe = min(lo + (lane + 1) * step, hi);
+        const bool le = probe < hi ? (__ldg(gstart + probe) <= t0) : false;
+        const int cnt = __popc(__ballot_sync(0xffffffffu, le)); // probes are ascending: the first cnt satisfy <=
+        const int nlo = lo + cnt * step, nhi = min(lo + (cnt + 1) * step, hi);
+        lo = cnt ? min(nlo, hi - 1) : lo;
+        hi = nhi;
+        if (lo >= hi) hi = lo + 1;
+    }
+    int lo_r = lo;
+    // lanes further right: walk forward (bounded), then finish with a plain binary search if rows are sparse
+    int steps = 0;
+    while (lo_r + 1 < nrows_grid && __ldg(gstart + lo_r + 1) <= t && steps < 8) { ++lo_r; ++steps; }
+    if (lo_r + 1 < nrows_grid && __ldg(gstart + lo_r + 1) <= t) {
+        int a = lo_r, b = nrows_grid;
+        while (b - a > 1) {
+            const int mid = (a + b) >> 1;
+            if (__ldg(gstart + mid) <= t) a = mid; else b = mid;
+        }
+        lo_r = a;
+    }
+    return lo_r;
+}
+
+// One candidate run of ONE target, scalar: the general path (crowded runs, targets whose row differs from
+// their thread-mates', array tails).  Adds the run's W terms (self included) to `sum` and writes the two mask
+// words of row r.
+template <bool kAux, bool kMask>
+__device__ __forceinline__ void density_row_single(const Consts& c, const float4* __restrict__ posm, unsigned int* __restrict__ mask,
+                                                   int n, int i, const float4& pi, int r, int jb, int je, float& sum) {
+    const int jm = min(je, jb + kMaskBits);
+    unsigned int m0 = 0, m1 = 0; // bits enter at the top and slide down: after len steps bit k = candidate k
+    int j = jb;
+    const int jh = min(jm, jb + 32);
+    for (; j < jh; j++) {
+        const float4 pj = ldg4(posm + j);
+        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
+        if (kMask) m0 = (m0 >> 1) | ((d2 < c.R2) ? 0x80000000u : 0u);
+    }
+    if (kMask) m0 = (jh - jb) ? (m0 >> (32 - (jh - jb))) : 0u;
+    for (; j < jm; j++) {
+        const float4 pj = ldg4(posm + j);
+        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        if (kAux) sum = fmaf(pj.w, w_shape(c, d2), sum);
+        if (kMask) m1 = (m1 >> 1) | ((d2 < c.R2) ? 0x80000000u : 0u);
+    }
+    if (kMask) m1 = (jm - jh) > 0 ? (m1 >> (32 - (jm - jh))) : 0u;
+    if (kAux)
+        for (; j < je; j++) { // beyond the mask: crowded run
+            const float4 pj = ldg4(posm + j);
+            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            sum = fmaf(pj.w, w_shape(c, fmaf(dx, dx, fmaf(dy, dy, dz * dz))), sum);
+        }
+    if (kMask) {
+        const int self = i - jb; // the self term is excluded by index (SphUtils.cpp:132,216)
+        if (self >= 0 && i < je) {
+            if (self < 32) m0 &= ~(1u << self);
+            else if (self < kMaskBits) m1 &= ~(1u << (self - 32));
+        }
+        mask[(size_t)(2 * r) * n + i] = m0;      // word w of row r covers candidates jb + 32*w ...
+        mask[(size_t)(2 * r + 1) * n + i] = m1;
+    }
+}
+
+// Density kernel proper.  Each thread owns kDT = 4 CONSECUTIVE sorted particles ("targets").  Neighbouring
+// slots are neighbouring particles, so the four share their candidate runs up to a cell or two in x: every
+// candidate is loaded once and tested against all four -- a quarter of the L1 wavefronts per test -- and the
+// four tests run as two packed-FP32 pairs (Blackwell FADD2 / FMUL2 / FFMA2: one issue slot, two lanes of
+// math), which is what this issue-bound loop needs (profiles/r1b: issue 83 %, L1 data pipe 75 %).
+//   u  = d2 - R^2            sign bit = "inside the support"  -> funnel-shifted straight into the mask word
+//   t  = -u / h^2 = h^2 - d2/h^2 ;  W ~ max(t, 0)^3
+// Union run of the four targets: [jb of the leftmost, je of the rightmost]; a candidate outside a target's own
+// run is at least R away from it in x, so its bit is (at most a rounding-level ~0 term) clear and the
+// per-target mask is the union mask shifted down by (own jb - union jb).
+// 8 resident blocks of 128 threads per SM (64 registers): measured best on B200 -- the loop is latency-bound,
+// so occupancy beats the few spilled words (1: 2.38 ms, 6: 2.41, 7: 2.21, 8: 2.16 ms per 16.7 M particles;
+// a register-staged software prefetch of the candidates bought nothing on top).
+#ifndef SPHB_DENSITY_MINBLOCKS
+#define SPHB_DENSITY_MINBLOCKS 8
+#endif
+template <bool kAux, bool kMask>
+__global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                 const int* __restrict__ gstart,
+                                                 const float4* __restrict__ posm, const float4* __restrict__ vel,
+                                                 float4* __restrict__ aux, float4* __restrict__ vr,
+                                                 unsigned int* __restrict__ mask, int n) {
+    const GridDesc g = *gd;
+    const int t_raw = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nrows_grid = g.dims[1] * g.dims[2];
+    const int ngroups = __ldg(gstart + nrows_grid);
+    if ((t_raw & ~31) >= ngroups) return;          // whole warp beyond the last group
+    const bool live = t_raw < ngroups;
+    const int t = live ? t_raw : ngroups - 1;       // spare lanes of the last warp shadow the last group (warp-wide votes below)
+    const int lo_r = find_row(gstart, nrows_grid, t);
+    if (!live) return;
+    const int row_end = __ldg(cell_start + (lo_r + 1) * g.dims[0]);
+    const int i0 = __ldg(cell_start + lo_r * g.dims[0]) + (t - __ldg(gstart + lo_r)) * kDT;
+    const int nt = min(kDT, row_end - i0); // the tail group of a row is short: extra targets repeat the last one
+    float4 pi[kDT];
+    int cx[kDT], cy[kDT], cz[kDT];
+#pragma unroll
+    for (int k = 0; k < kDT; k++) {
+        pi[k] = ldg4(posm + i0 + min(k, nt - 1));
+        cell_key(g, pi[k].x, pi[k].y, pi[k].z, cx[k], cy[k], cz[k]);
+    }
+    const int S = g.stencil, Sx = g.stencil_x;
+    const int nrows = (2 * S + 1) * (2 * S + 1);
+    float sum[kDT] = {0.0f, 0.0f, 0.0f, 0.0f};
+    {
+        const int cxlo = min(min(cx[0], cx[1]), min(cx[2], cx[3])), cxhi = max(max(cx[0], cx[1]), max(cx[2], cx[3]));
+        const float2 nx01 = make_float2(-pi[0].x, -pi[1].x), ny01 = make_float2(-pi[0].y, -pi[1].y), nz01 = make_float2(-pi[0].z, -pi[1].z);
+        const float2 nx23 = make_float2(-pi[2].x, -pi[3].x), ny23 = make_float2(-pi[2].y, -pi[3].y), nz23 = make_float2(-pi[2].z, -pi[3].z);
+        const float2 nR2 = make_float2(-c.R2, -c.R2), nih2 = make_float2(-c.inv_h2, -c.inv_h2);
+        float2 acc01 = make_float2(0.0f, 0.0f), acc23 = make_float2(0.0f, 0.0f);
+        const int W = 2 * S + 1;
+        for (int r = 0; r < nrows; r++) {
+            const int z = cz[0] + r / W - S, y = cy[0] + r % W - S;
+            int jbu = 0, jeu = 0, jbk[kDT] = {0, 0, 0, 0};
+            const bool inside = !(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]);
+            if (inside) {
+                const int row = g.dims[0] * (y + g.dims[1] * z);
+                jbu = __ldg(cell_start + row + max(cxlo - Sx, 0));
+                jeu = __ldg(cell_start + row + min(cxhi + Sx, g.dims[0] - 1) + 1);
+#pragma unroll
+                for (int k = 0; k < kDT; k++) jbk[k] = (cx[k] == cxlo) ? jbu : __ldg(cell_start + row + max(cx[k] - Sx, 0));
+            }
+            if (jeu - jbu > kMaskBits) { // crowded union: per-target general path for this row
+#pragma unroll
+                for (int k = 0; k < kDT; k++) {
+                    if (k >= nt) break;
+                    int jb, je;
+                    row_run(g, cell_start, cx[k], cy[k], cz[k], r, jb, je);
+                    density_row_single<kAux, kMask>(c, posm, mask, n, i0 + k, pi[k], r, jb, je, sum[k]);
+                }
+                continue;
+            }
+            unsigned int mw[2][kDT];
+#pragma unroll
+            for (int w = 0; w < 2; w++) {
+                const int ja = min(jeu, jbu + 32 * w), jz = min(jeu, jbu + 32 * (w + 1));
+                unsigned int m[kDT] = {0u, 0u, 0u, 0u};
+#pragma unroll 2
+                for (int j = ja; j < jz; j++) {
+                    const float4 pj = ldg4(posm + j);
+                    const float2 xx = make_float2(pj.x, pj.x), yy = make_float2(pj.y, pj.y), zz = make_float2(pj.z, pj.z), mm = make_float2(pj.w, pj.w);
+                    {
+                        const float2 dx = __fadd2_rn(xx, nx01), dy = __fadd2_rn(yy, ny01), dz = __fadd2_rn(zz, nz01);
+                        const float2 d2 = __ffma2_rn(dx, dx, __ffma2_rn(dy, dy, __fmul2_rn(dz, dz)));
+                        const float2 u = __fadd2_rn(d2, nR2);
+                        if (kMask) {
+                            m[0] = __funnelshift_l(__float_as_uint(u.x), m[0], 1);
+                            m[1] = __funnelshift_l(__float_as_uint(u.y), m[1], 1);
+                        }
+                        if (kAux) {
+                            float2 t = __fmul2_rn(u, nih2);
+                            t.x = fmaxf(t.x, 0.0f);
+                            t.y = fmaxf(t.y, 0.0f);
+                            acc01 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc01);
+                        }
+                    }
+                    {
+                        const float2 dx = __fadd2_rn(xx, nx23), dy = __fadd2_rn(yy, ny23), dz = __fadd2_rn(zz, nz23);
+                        const float2 d2 = __ffma2_rn(dx, dx, __ffma2_rn(dy, dy, __fmul2_rn(dz, dz)));
+                        const float2 u = __fadd2_rn(d2, nR2);
+                        if (kMask) {
+                            m[2] = __funnelshift_l(__float_as_uint(u.x), m[2], 1);
+                            m[3] = __funnelshift_l(__float_as_uint(u.y), m[3], 1);
+                        }
+                        if (kAux) {
+                            float2 t = __fmul2_rn(u, nih2);
+                            t.x = fmaxf(t.x, 0.0f);
+                            t.y = fmaxf(t.y, 0.0f);
+                            acc23 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc23);
+                        }
+                    }
+                }
+                // the bits went in newest-lowest: candidate q of this word sits at bit (len-1-q); put it at bit q
+                const int len = jz - ja;
+#pragma unroll
+                for (int k = 0; k < kDT; k++) mw[w][k] = len ? (__brev(m[k]) >> (32 - len)) : 0u;
+            }
+            if (kMask) {
+#pragma unroll
+                for (int k = 0; k < kDT; k++) {
+                    unsigned long long m64 = ((unsigned long long)mw[1][k] << 32) | mw[0][k];
+                    m64 >>= (jbk[k] - jbu); // union-relative -> relative to this target's own run
+                    const int self = i0 + k - jbk[k];
+                    if (r == (nrows >> 1) && self >= 0 && self < kMaskBits) m64 &= ~(1ull << self); // self excluded by index
+                    if (k < nt) {
+                        mask[(size_t)(2 * r) * n + i0 + k] = (unsigned int)m64;
+                        mask[(size_t)(2 * r + 1) * n + i0 + k] = (unsigned int)(m64 >> 32);
+                    }
+                }
+            }
+        }
+        sum[0] += acc01.x; sum[1] += acc01.y; sum[2] += acc23.x; sum[3] += acc23.y;
+    }
+    if (kAux) {
+#pragma unroll
+        for (int k = 0; k < kDT; k++) {
+            if (k >= nt) break;
+            // self term: the runs above included j == i exactly once (its own cell's row); take it out again
+            const float s = sum[k] - pi[k].w * (c.h2 * c.h2 * c.h2);
+            const float4 a = finish_density(c, s);
+            aux[i0 + k] = a;
+            // the force kernel gathers two records per neighbour: posm and (vx, vy, vz, rho); P, sqrt|P/rho| and
+            // 1/rho are functions of rho and are recomputed there (two gathers instead of three: the kernel is
+            // bound by L1 gather wavefronts, profiles/r1b)
+            const float4 v = ldg4(vel + i0 + k);
+            vr[i0 + k] = make_float4(v.x, v.y, v.z, a.x);
+        }
+    }
+}
+
+} // namespace sphb
