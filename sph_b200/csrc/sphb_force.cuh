@@ -12,8 +12,8 @@ namespace sphb {
 
 // One pair (i <- j), in range (d2 < R2), accumulates the direction-weighted scalar; the factor
 // Kg = -45/(pi h^6) is applied once after the sum.
-__device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, float dz, float d2, const float4& vi, const float4& ai,
-                                           float mj, const float4& vj, const float4& aj, float& ax, float& ay, float& az) {
+__device__ __forceinline__ float pair_weight(const Consts& c, float dx, float dy, float dz, float d2, const float4& vi, const float4& ai,
+                                             float mj, const float4& vj, const float4& aj) {
     const float vdotr = fmaf(vi.x - vj.x, dx, fmaf(vi.y - vj.y, dy, (vi.z - vj.z) * dz)); // :220
     const float rinv = fast_rsqrt(d2);
     const float r = d2 * rinv;
@@ -26,7 +26,12 @@ __device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, 
     }
     // :228  -(m_j) * (pi + (P_i + P_j) / (2 rho_j rho_i)); ai.w, aj.w = 1/rho
     const float t = -mj * fmaf(0.5f * (ai.y + aj.y), ai.w * aj.w, visc);
-    const float wgt = t * s * s * rinv; // times (x_i - x_j) = temp * |gradW| * normalize(i - j) / Kg
+    return t * s * s * rinv; // times (x_i - x_j) = temp * |gradW| * normalize(i - j) / Kg
+}
+
+__device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, float dz, float d2, const float4& vi, const float4& ai,
+                                           float mj, const float4& vj, const float4& aj, float& ax, float& ay, float& az) {
+    const float wgt = pair_weight(c, dx, dy, dz, d2, vi, ai, mj, vj, aj);
     ax = fmaf(wgt, dx, ax);
     ay = fmaf(wgt, dy, ay);
     az = fmaf(wgt, dz, az);
@@ -102,15 +107,42 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
         bool crowded = false;
         int nw = 0;
+        if (kRows == 9) {
+            // All 18 mask words and all 18 run bounds are requested before the first is consumed (one round trip to
+            // L2 each instead of nine: row_run's early return for rows outside the grid keeps the compiler from
+            // hoisting the loads itself).  A row outside the grid reads a clamped row and is emptied afterwards.
+            unsigned int mw[18];
+            int jbr[9], jer[9];
 #pragma unroll
-        for (int r = 0; r < kRows; r++) {
-            int jb, je;
-            row_run(g, cell_start, cx, cy, cz, r, jb, je);
-            const unsigned int m0 = mask[(size_t)(2 * r) * n + i], m1 = mask[(size_t)(2 * r + 1) * n + i];
-            s_jb[r][tid] = jb;
-            if (m0) { s_word[nw][tid] = m0; s_idx[nw][tid] = (unsigned char)(2 * r); nw++; }
-            if (m1) { s_word[nw][tid] = m1; s_idx[nw][tid] = (unsigned char)(2 * r + 1); nw++; }
-            crowded |= (je - jb) > kMaskBits;
+            for (int w = 0; w < 18; w++) mw[w] = __ldg(mask + (size_t)w * n + i);
+            const int x0 = max(cx - g.stencil_x, 0), x1 = min(cx + g.stencil_x, g.dims[0] - 1) + 1;
+#pragma unroll
+            for (int r = 0; r < 9; r++) {
+                const int zc = min(max(cz + r / 3 - 1, 0), g.dims[2] - 1), yc = min(max(cy + r % 3 - 1, 0), g.dims[1] - 1);
+                const int row = g.dims[0] * (yc + g.dims[1] * zc);
+                jbr[r] = __ldg(cell_start + row + x0);
+                jer[r] = __ldg(cell_start + row + x1);
+            }
+#pragma unroll
+            for (int r = 0; r < 9; r++) {
+                const int z = cz + r / 3 - 1, y = cy + r % 3 - 1;
+                if (z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]) jbr[r] = jer[r] = 0;
+                s_jb[r][tid] = jbr[r];
+                if (mw[2 * r]) { s_word[nw][tid] = mw[2 * r]; s_idx[nw][tid] = (unsigned char)(2 * r); nw++; }
+                if (mw[2 * r + 1]) { s_word[nw][tid] = mw[2 * r + 1]; s_idx[nw][tid] = (unsigned char)(2 * r + 1); nw++; }
+                crowded |= (jer[r] - jbr[r]) > kMaskBits;
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < kRows; r++) {
+                int jb, je;
+                row_run(g, cell_start, cx, cy, cz, r, jb, je);
+                const unsigned int m0 = mask[(size_t)(2 * r) * n + i], m1 = mask[(size_t)(2 * r + 1) * n + i];
+                s_jb[r][tid] = jb;
+                if (m0) { s_word[nw][tid] = m0; s_idx[nw][tid] = (unsigned char)(2 * r); nw++; }
+                if (m1) { s_word[nw][tid] = m1; s_idx[nw][tid] = (unsigned char)(2 * r + 1); nw++; }
+                crowded |= (je - jb) > kMaskBits;
+            }
         }
         float ax = 0.0f, ay = 0.0f, az = 0.0f;
         // One neighbour per lane per iteration: a lane whose word ran dry steps to its next (non-empty) word first,
