@@ -270,9 +270,12 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
         const float2 nx23 = make_float2(-pi[2].x, -pi[3].x), ny23 = make_float2(-pi[2].y, -pi[3].y), nz23 = make_float2(-pi[2].z, -pi[3].z);
         const float2 nR2 = make_float2(-c.R2, -c.R2), nih2 = make_float2(-c.inv_h2, -c.inv_h2);
         float2 acc01 = make_float2(0.0f, 0.0f), acc23 = make_float2(0.0f, 0.0f);
-        const int W = 2 * S + 1;
-        for (int r = 0; r < nrows; r++) {
-            const int z = cz[0] + r / W - S, y = cy[0] + r % W - S;
+        // rows in canonical order r = (dz+S)*(2S+1) + (dy+S), counted without the divisions a runtime stencil would cost
+        int dy_r = -S, dz_r = -S;
+        unsigned int* mrow = mask + i0; // word w of row r of target k: mrow[(2r+w)*n + k], advanced row by row
+        for (int r = 0; r < nrows; r++, mrow += 2 * (size_t)n) {
+            const int z = cz[0] + dz_r, y = cy[0] + dy_r;
+            if (++dy_r > S) { dy_r = -S; ++dz_r; }
             int jbu = 0, jeu = 0, jbk[kDT] = {0, 0, 0, 0};
             const bool inside = !(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]);
             if (inside) {
@@ -297,10 +300,11 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
             for (int w = 0; w < 2; w++) {
                 const int ja = min(jeu, jbu + 32 * w), jz = min(jeu, jbu + 32 * (w + 1));
                 unsigned int m[kDT] = {0u, 0u, 0u, 0u};
-#pragma unroll 2
-                for (int j = ja; j < jz; j++) {
-                    const float4 pj = ldg4(posm + j);
-                    const float2 xx = make_float2(pj.x, pj.x), yy = make_float2(pj.y, pj.y), zz = make_float2(pj.z, pj.z), mm = make_float2(pj.w, pj.w);
+                // Candidates two at a time; an odd run repeats its last candidate with mass 0 (adds exactly 0, and its
+                // duplicate mask bit is dropped below) instead of paying a separate tail loop that some lane of the
+                // warp would take in nearly every row.
+                auto test4 = [&](const float4& pj, float mj) {
+                    const float2 xx = make_float2(pj.x, pj.x), yy = make_float2(pj.y, pj.y), zz = make_float2(pj.z, pj.z), mm = make_float2(mj, mj);
                     {
                         const float2 dx = __fadd2_rn(xx, nx01), dy = __fadd2_rn(yy, ny01), dz = __fadd2_rn(zz, nz01);
                         const float2 d2 = __ffma2_rn(dx, dx, __ffma2_rn(dy, dy, __fmul2_rn(dz, dz)));
@@ -331,9 +335,19 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
                             acc23 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc23);
                         }
                     }
+                };
+                const int len = jz - ja;
+                for (int j = ja; j < jz; j += 2) {
+                    const bool two = j + 1 < jz;
+                    const float4 p0 = ldg4(posm + j), p1 = ldg4(posm + (two ? j + 1 : j));
+                    test4(p0, p0.w);
+                    test4(p1, two ? p1.w : 0.0f);
+                }
+                if (kMask && (len & 1)) {
+#pragma unroll
+                    for (int k = 0; k < kDT; k++) m[k] >>= 1;
                 }
                 // the bits went in newest-lowest: candidate q of this word sits at bit (len-1-q); put it at bit q
-                const int len = jz - ja;
 #pragma unroll
                 for (int k = 0; k < kDT; k++) mw[w][k] = len ? (__brev(m[k]) >> (32 - len)) : 0u;
             }
@@ -345,8 +359,8 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
                     const int self = i0 + k - jbk[k];
                     if (r == (nrows >> 1) && self >= 0 && self < kMaskBits) m64 &= ~(1ull << self); // self excluded by index
                     if (k < nt) {
-                        mask[(size_t)(2 * r) * n + i0 + k] = (unsigned int)m64;
-                        mask[(size_t)(2 * r + 1) * n + i0 + k] = (unsigned int)(m64 >> 32);
+                        mrow[k] = (unsigned int)m64;
+                        mrow[(size_t)n + k] = (unsigned int)(m64 >> 32);
                     }
                 }
             }

@@ -232,6 +232,47 @@ def test_forces_end_to_end_own_density(eng, oracle, golden):
     assert normd <= 2e-3
 
 
+@pytest.mark.parametrize("h,rho0,c,dt,eps", [(0.3, 6.0, 50.0, 0.01, 0.02), (0.6, 20.0, 100.0, 0.02, 0.005)])
+def test_other_constructor_parameters_and_unequal_masses(h, rho0, c, dt, eps):
+    """SphUtils(h, rho0, c, dt, eps) with values other than main.cpp:62's, particle masses spread over
+    [0.5, 1.5] x the scene's, non-zero velocities (so the viscosity branch runs): density, acceleration fed the
+    oracle's rho and P, and the bit-exact integration + walls, all against the oracle's all-pairs loops."""
+    from oracle.oracle import Oracle
+    orc = Oracle(h=h, rho0=rho0, c=c, dt=dt, eps=eps)
+    R = float(np.float32(h) * np.float32(h))
+    pos, vel = scenes.lattice_block(14, 18, 12, 0.40 * R, (0.1, 0.1, 0.1), seed=77, jitter=0.25, vel_amp=0.3 * R / dt)
+    ps = scenes.make_particles(pos, vel, h=h, rho0=rho0, eps=eps)
+    ps["mass"] *= (0.5 + scenes.hash_uniform(5, np.arange(len(ps), dtype=np.uint64), 0, 3)).astype(np.float32)
+    walls = scenes.tank_walls(40 * R, 10 * R)
+    with sph_b200.Engine(h=h, rho0=rho0, c=c, dt=dt, eps=eps) as e:
+        e.set_walls(walls)
+        want = ps.copy()
+        orc.update_density(want)
+        got = ps.copy()
+        e.upload(got)
+        e.update_density()
+        e.download(got, F_DENSITY)
+        assert rel_rho(got["density"], want["density"]) <= RHO_TOL
+        assert (want["density"] > np.float32(rho0)).mean() > 0.3      # not all clamped: the sum itself is compared
+        fed = want.copy()                                              # forces from the oracle's rho, P
+        orc.update_forces(want)
+        e.upload(fed)
+        e.update_forces()
+        e.download(fed, sph_b200.F_ACCEL)
+        plain, normd = accel_errors(fed["accel"], want["accel"], sum_abs_terms(orc, want))
+        print(f"h={h}: accel error plain-relative {plain:.3e}, normalised {normd:.3e}")
+        assert normd <= ACC_TOL
+        got = want.copy()                                              # integrate + walls from the oracle's accel
+        orc.update_posvel(want)
+        orc.collision(want, walls)
+        e.upload(got)
+        e.update_posvel()
+        e.collision()
+        e.download(got, F_ALL)
+        for f in ("pos", "vel"):
+            assert np.array_equal(got[f], want[f]), f
+
+
 def test_pair_force_antisymmetry(eng):
     """sum_i m_i a_i(pair part) ~ 0 for equal masses."""
     ps, _ = scenes.dam_break(16, 16, 16, stressed=True)
