@@ -92,9 +92,14 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
                                                const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
                                                float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                BBoxAcc* bbox, int n) {
-    __shared__ unsigned int s_word[2 * kRows][128];  // this thread's NON-EMPTY mask words, compacted ...
-    __shared__ unsigned char s_idx[2 * kRows][128];  // ... which word each is (2*row + half) ...
-    __shared__ int s_jb[kRows][128];                 // ... and where each row's run starts
+    // kRows == 9: this thread's NON-EMPTY mask words, compacted, each with the sorted slot of its bit 0 -- one LDS.64 per
+    // refill.  kRows == 25 would need 51 KB that way (static shared memory ends at 48 KB): there the words are kept with
+    // their index (2*row + half) and the rows' run starts separately.
+    constexpr bool kPairs = kRows == 9;
+    __shared__ uint2 s_wb[kPairs ? 2 * kRows : 1][128];
+    __shared__ unsigned int s_word[kPairs ? 1 : 2 * kRows][128];
+    __shared__ unsigned char s_idx[kPairs ? 1 : 2 * kRows][128];
+    __shared__ int s_jb[kPairs ? 1 : kRows][128];
     const int tid = threadIdx.x;
     const int i = blockIdx.x * blockDim.x + tid;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -127,9 +132,8 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             for (int r = 0; r < 9; r++) {
                 const int z = cz + r / 3 - 1, y = cy + r % 3 - 1;
                 if (z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]) jbr[r] = jer[r] = 0;
-                s_jb[r][tid] = jbr[r];
-                if (mw[2 * r]) { s_word[nw][tid] = mw[2 * r]; s_idx[nw][tid] = (unsigned char)(2 * r); nw++; }
-                if (mw[2 * r + 1]) { s_word[nw][tid] = mw[2 * r + 1]; s_idx[nw][tid] = (unsigned char)(2 * r + 1); nw++; }
+                if (mw[2 * r]) { s_wb[nw][tid] = make_uint2(mw[2 * r], (unsigned int)jbr[r]); nw++; }
+                if (mw[2 * r + 1]) { s_wb[nw][tid] = make_uint2(mw[2 * r + 1], (unsigned int)(jbr[r] + 32)); nw++; }
                 crowded |= (jer[r] - jbr[r]) > kMaskBits;
             }
         } else {
@@ -152,9 +156,15 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         for (;;) {
             if (m == 0) {
                 if (++k >= nw) break;
-                m = s_word[k][tid];
-                const int w = s_idx[k][tid];
-                jb = s_jb[w >> 1][tid] + ((w & 1) << 5);
+                if (kPairs) {
+                    const uint2 wb = s_wb[k][tid];
+                    m = wb.x;
+                    jb = (int)wb.y;
+                } else {
+                    m = s_word[k][tid];
+                    const int w = s_idx[k][tid];
+                    jb = s_jb[w >> 1][tid] + ((w & 1) << 5);
+                }
             }
             const int j = jb + __ffs((int)m) - 1;
             m &= m - 1;
