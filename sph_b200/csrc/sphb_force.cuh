@@ -74,6 +74,9 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
     }
 }
 
+#ifndef SPHB_FORCE_WORDS
+#define SPHB_FORCE_WORDS 13
+#endif
 // kFused: also integrate + collide and write the new state to the other buffer (ping-pong: every
 //         thread reads only old buffers, so the fusion is race-free).
 // kBBox:  also fold the new positions into the bounding box for the next step's grid.
@@ -96,7 +99,13 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
     // refill.  kRows == 25 would need 51 KB that way (static shared memory ends at 48 KB): there the words are kept with
     // their index (2*row + half) and the rows' run starts separately.
     constexpr bool kPairs = kRows == 9;
-    __shared__ uint2 s_wb[kPairs ? 2 * kRows : 1][128];
+    // Only the first kCapW non-empty words of a thread are staged: every KB of shared memory is a KB less L1 for the
+    // gathers this kernel lives on (4 KB more per block cost 8 % in time).  13 words = 13.3 KB per block is the most
+    // that keeps the 9 resident blocks (56 registers) inside the 132 KB shared-memory carve-out, i.e. L1 at 124 KB:
+    // measured 8 / 10 / 11 / 12 / 13 / 14 / 18 words -> 2.23 / 2.21 / 2.23 / 2.11 / 2.12 / 2.25 / 2.28 ms.  A thread with
+    // more non-empty words (rare) reads the rest straight from the mask array after the main walk -- same order.
+    constexpr int kCapW = kPairs ? SPHB_FORCE_WORDS : 1;
+    __shared__ uint2 s_wb[kCapW][128];
     __shared__ unsigned int s_word[kPairs ? 1 : 2 * kRows][128];
     __shared__ unsigned char s_idx[kPairs ? 1 : 2 * kRows][128];
     __shared__ int s_jb[kPairs ? 1 : kRows][128];
@@ -111,7 +120,7 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         int cx, cy, cz;
         cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);
         bool crowded = false;
-        int nw = 0;
+        int nw = 0, first_over = 2 * kRows;
         if (kRows == 9) {
             // All 18 mask words and all 18 run bounds are requested before the first is consumed (one round trip to
             // L2 each instead of nine: row_run's early return for rows outside the grid keeps the compiler from
@@ -132,8 +141,16 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             for (int r = 0; r < 9; r++) {
                 const int z = cz + r / 3 - 1, y = cy + r % 3 - 1;
                 if (z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]) jbr[r] = jer[r] = 0;
-                if (mw[2 * r]) { s_wb[nw][tid] = make_uint2(mw[2 * r], (unsigned int)jbr[r]); nw++; }
-                if (mw[2 * r + 1]) { s_wb[nw][tid] = make_uint2(mw[2 * r + 1], (unsigned int)(jbr[r] + 32)); nw++; }
+                if (mw[2 * r]) {
+                    if (nw < kCapW) s_wb[nw][tid] = make_uint2(mw[2 * r], (unsigned int)jbr[r]);
+                    else if (nw == kCapW) first_over = 2 * r;
+                    nw++;
+                }
+                if (mw[2 * r + 1]) {
+                    if (nw < kCapW) s_wb[nw][tid] = make_uint2(mw[2 * r + 1], (unsigned int)(jbr[r] + 32));
+                    else if (nw == kCapW) first_over = 2 * r + 1;
+                    nw++;
+                }
                 crowded |= (jer[r] - jbr[r]) > kMaskBits;
             }
         } else {
@@ -153,21 +170,7 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         // so the lanes of a warp stay in lockstep on the pair body until their lists end.
         int k = -1, jb = 0;
         unsigned int m = 0;
-        for (;;) {
-            if (m == 0) {
-                if (++k >= nw) break;
-                if (kPairs) {
-                    const uint2 wb = s_wb[k][tid];
-                    m = wb.x;
-                    jb = (int)wb.y;
-                } else {
-                    m = s_word[k][tid];
-                    const int w = s_idx[k][tid];
-                    jb = s_jb[w >> 1][tid] + ((w & 1) << 5);
-                }
-            }
-            const int j = jb + __ffs((int)m) - 1;
-            m &= m - 1;
+        auto visit = [&](int j) {
             const float4 pj = ldg4(posm + j);
             float4 vj, aj;
             if (kDerive) {
@@ -180,6 +183,37 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
             const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
             pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, vj, aj, ax, ay, az);
+        };
+        const int nstaged = kPairs ? min(nw, kCapW) : nw;
+        for (;;) {
+            if (m == 0) {
+                if (++k >= nstaged) break;
+                if (kPairs) {
+                    const uint2 wb = s_wb[k][tid];
+                    m = wb.x;
+                    jb = (int)wb.y;
+                } else {
+                    m = s_word[k][tid];
+                    const int w = s_idx[k][tid];
+                    jb = s_jb[w >> 1][tid] + ((w & 1) << 5);
+                }
+            }
+            const int j = jb + __ffs((int)m) - 1;
+            m &= m - 1;
+            visit(j);
+        }
+        if (kPairs && nw > kCapW) { // the words that did not fit the staging area, in the same order
+            for (int ww = first_over; ww < 2 * kRows; ww++) {
+                unsigned int mo = __ldg(mask + (size_t)ww * n + i);
+                if (!mo) continue;
+                int jb2, je2;
+                row_run(g, cell_start, cx, cy, cz, ww >> 1, jb2, je2);
+                jb2 += (ww & 1) << 5;
+                while (mo) {
+                    visit(jb2 + __ffs((int)mo) - 1);
+                    mo &= mo - 1;
+                }
+            }
         }
         if (crowded) { // candidates past the 64th of a run: test them here (rare)
             for (int rr = 0; rr < kRows; rr++) {

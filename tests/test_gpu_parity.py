@@ -327,6 +327,33 @@ def test_crowded_runs_beyond_the_mask(eng, oracle):
     assert normd <= 2e-3
 
 
+def test_many_mask_words_overflow_the_staging_area(oracle):
+    """Runs of 33..64 candidates: most of a particle's 18 mask words are non-empty, more than the force kernel stages
+    in shared memory (SPHB_FORCE_WORDS = 13), so the rest is read back from the mask array.  Cubic cells
+    (cell_x_div 1) and a lattice 1.8x denser than main.cpp's give ~45 candidates per run."""
+    pos, vel = scenes.lattice_block(22, 22, 22, 0.082, (0.3, 0.3, 0.3), seed=3, jitter=0.3, vel_amp=0.5)
+    ps = scenes.make_particles(pos, vel)
+    R = 0.45 * 0.45
+    runs = np.histogramdd(pos.astype(np.float64), bins=[np.arange(0.3, 2.2, 3 * R)] + [np.arange(0.3, 2.2, R)] * 2)[0]
+    assert 33 <= np.median(runs[runs > 0]) <= 64                   # typical run: both words of a row in use, no overflow of the mask
+    want = ps.copy()
+    oracle.update_density(want, cells=True)
+    fed = want.copy()
+    oracle.update_forces(want, cells=True)
+    with sph_b200.Engine(cell_x_div=1) as e:
+        e.upload(ps); e.update_density(); e.download(ps, F_DENSITY)
+        assert rel_rho(ps["density"], want["density"]) <= RHO_TOL
+        e.upload(fed); e.update_forces(); e.download(fed, sph_b200.F_ACCEL)
+        _, normd = accel_errors(fed["accel"], want["accel"], sum_abs_terms(oracle, want))
+        assert normd <= ACC_TOL
+        ps2 = ps.copy()                                             # and through the fused step kernel
+        e.upload(ps2); e.step(1); e.download(ps2, F_ALL)
+        ps3 = ps.copy()
+        e.upload(ps3); e.update_density(); e.update_forces(); e.update_posvel(); e.collision(); e.download(ps3, F_ALL)
+        for f in ("pos", "vel", "accel"):
+            assert np.array_equal(ps2[f], ps3[f]), f
+
+
 # --------------------------------------------------------------------------------------------------
 # integration and walls: bit-exact given the same inputs
 
