@@ -257,12 +257,15 @@ int sphb_reserve(sphb_engine* e, size_t n_max);
 
 /* Classify the particles this rank owned by their current x: the ones it keeps (as owned or as ghosts) are
  * compacted into the engine's spare buffers, the ones a neighbour needs (its ghost zone, and migrants) into
- * msg_left / msg_right (either may be NULL when that neighbour does not exist).  Previous ghosts are dropped.
- * Deterministic (order-preserving compaction).  Asynchronous on the engine's stream. */
+ * msg_left / msg_right (either may be NULL when that neighbour does not exist).  Previous ghosts are dropped
+ * (marked dead in place; a negative mass means "dead" to an engine that has used sphb_mg_pack).
+ * Deterministic (order-preserving compaction of the messages).  Asynchronous on the engine's stream. */
 int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* msg_right, size_t capacity);
 
 /* Append what the neighbours sent (NULL = none), refresh the ownership flags and adopt the new particle
- * set.  Synchronises once to read the counts.  counts[4] (may be NULL) = {kept, from_left, from_right, total}.
+ * set.  Synchronises once to read the counts.  counts[4] (may be NULL) = {records before the messages (the dropped
+ * ones stay in the arrays, marked dead with mass -1, until the next step's sort removes them -- reserve room for
+ * them), from_left, from_right, total}.  sphb_count() excludes the dead again after the next step.
  * SPHB_ERR_CAPACITY if a sender overflowed its message or the arrays reserved with sphb_reserve are full. */
 int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, size_t counts[4]);
 

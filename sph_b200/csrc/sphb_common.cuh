@@ -11,11 +11,17 @@ constexpr int kMaxWalls = 16;
 constexpr int kMaxRows = 1 << 22; // cap on dims[1]*dims[2] ((y,z) rows of cells): bounds the row-group table
 
 // Device-resident description of the uniform grid (rebuilt every step by k_grid_setup).
+// Bins behind the last cell for records the multi-GPU exchange marked dead (mass < 0): the counting sort files them
+// after every live particle, which removes them without a compaction pass of its own.  Several bins, so that their
+// histogram atomics do not all hit one address.
+constexpr int kTrashBins = 1024;
+
 struct GridDesc {
     float origin[3];
     float cell[3]; // per axis (equal unless an axis is periodic and the cell was stretched to tile it)
     int dims[3];
     int ncell;     // dims[0]*dims[1]*dims[2]
+    int nbins;     // ncell + kTrashBins: counters / scan length (the extra bins collect records marked dead, see k_key_hist)
     int stencil;   // half width of the stencil in y and z cells: ceil(R / cell) (1 when cell >= R)
     int stencil_x; // half width in x cells: ceil(R / cell_x)
 };

@@ -15,7 +15,7 @@ __global__ void __launch_bounds__(256) k_scatter(const int* __restrict__ key, co
                                                  const int* __restrict__ cell_start, int2* __restrict__ pairs, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    pairs[cell_start[key[i]] + slot[i]] = make_int2(oid[i], i);
+    pairs[cell_start[key[i]] + slot[i]] = make_int2(oid ? oid[i] : i, i); // oid == nullptr: ids are the slot numbers
 }
 
 // A cell that holds more than this many particles (a clamped boundary cell full of strays, or everything gone
@@ -29,11 +29,12 @@ __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pa
                                                      const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                      float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                      float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                     int* __restrict__ oid_out, int n) {
+                                                     int* __restrict__ oid_out, int n, const GridDesc* __restrict__ gd) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int2 me = pairs[p];
     const int k = key[me.y];
+    if (k >= gd->ncell) return; // a trash bin: records the slab exchange marked dead end here and are not carried over
     const int b = cell_start[k], e = cell_start[k + 1];
     int rank = 0;
     if (e - b <= kStableRankLimit) {

@@ -88,6 +88,8 @@ struct sphb_engine {
     long long max_cells = 0;
 
     bool have_state = false;
+    bool oid_identity = false; // after sphb_mg_unpack: original id == slot; oid[cur] is only written when somebody needs it
+    size_t n_dead = 0;       // records among the n that sphb_mg_pack marked dead (mass -1): the next sort files them last and drops them
     bool grid_valid = false; // cell_start / sorted order correspond to the current positions
     bool bbox_valid = false; // d_bbox holds the bbox of the current positions
     bool mask_valid = false; // neighbour masks correspond to the current sorted positions
@@ -111,6 +113,16 @@ namespace {
 
 int use_device(sphb_engine* e) {
     CK(cudaSetDevice(e->device));
+    return SPHB_OK;
+}
+
+// oid[cur] as an array (see oid_identity)
+int ensure_oid(sphb_engine* e) {
+    if (e->oid_identity && e->n) {
+        LAUNCH(e, k_fill_iota, cdiv(e->n, 256), 256, 0, e->oid[e->cur].p, (int)e->n);
+        CK(cudaGetLastError());
+    }
+    e->oid_identity = false;
     return SPHB_OK;
 }
 
@@ -174,8 +186,8 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)div * (long long)(2 * want + 65536);
     if (mc > (1ll << 30)) mc = 1ll << 30;
     if (mc > e->max_cells) {
-        CK(e->cell_start.reserve((size_t)mc + 2));
-        CK(e->block_sums.reserve((size_t)cdiv(mc + 2, kScanTile) + 1));
+        CK(e->cell_start.reserve((size_t)mc + 2 + kTrashBins));
+        CK(e->block_sums.reserve((size_t)cdiv(mc + 2 + kTrashBins, kScanTile) + 1));
         CK(e->row_groups.reserve((size_t)(mc + 2 < kMaxRows + 2 ? mc + 2 : kMaxRows + 2)));
         e->max_cells = mc;
     }
@@ -204,26 +216,29 @@ int run_sort(sphb_engine* e, bool carry_all) {
         if (rc) return rc;
     }
     const int cur = e->cur, nxt = cur ^ 1;
-    const int ntile_cap = cdiv(e->max_cells + 1, kScanTile);
-    int setup_blocks = cdiv(e->max_cells + 1, 256 * 8);
+    const int ntile_cap = cdiv(e->max_cells + 1 + kTrashBins, kScanTile);
+    int setup_blocks = cdiv(e->max_cells + 1 + kTrashBins, 256 * 8);
     if (setup_blocks > 148 * 8) setup_blocks = 148 * 8;
     LAUNCH(e, k_grid_setup, setup_blocks, 256, 0, e->c, e->d_bbox, e->d_grid, e->cell_start.p);
     const int pb = cdiv(n, 256);
     LAUNCH(e, k_key_hist, pb, 256, 0, e->d_grid, e->posm[cur].p, n, e->key.p, e->slot.p, e->cell_start.p, e->d_bbox,
-           e->c.domain_fixed ? 0 : 1);
+           e->c.domain_fixed ? 0 : 1, e->n_dead ? 1 : 0);
     LAUNCH(e, k_scan_reduce, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
     LAUNCH(e, k_scan_top, 1, kScanThreads, 0, e->d_grid, e->block_sums.p);
     LAUNCH(e, k_scan_apply, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
     LAUNCH(e, k_row_groups, 1, kRgThreads, 0, e->d_grid, e->cell_start.p, e->row_groups.p);
-    LAUNCH(e, k_scatter, pb, 256, 0, e->key.p, e->slot.p, e->oid[cur].p, e->cell_start.p, e->pairs.p, n);
+    LAUNCH(e, k_scatter, pb, 256, 0, e->key.p, e->slot.p, e->oid_identity ? (const int*)nullptr : e->oid[cur].p, e->cell_start.p, e->pairs.p, n);
+    e->oid_identity = false; // k_rank_gather writes the new buffer's ids
     if (carry_all)
         LAUNCH(e, k_rank_gather<true>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n);
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid);
     else
         LAUNCH(e, k_rank_gather<false>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n);
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid);
     CK(cudaGetLastError());
     e->cur = nxt;
+    e->n -= e->n_dead; // the dead records now sit behind the live ones: [n, n + n_dead) of the new buffers, never read again
+    e->n_dead = 0;
     e->grid_valid = true;
     e->mask_valid = false;
     e->vr_valid = false;
@@ -234,6 +249,7 @@ int run_sort(sphb_engine* e, bool carry_all) {
 // K4.  with_aux = false only rebuilds the neighbour masks (update_forces on an uploaded rho/P).
 int run_density(sphb_engine* e, bool with_aux) {
     const int n = (int)e->n;
+    if (n == 0) return SPHB_OK;
     auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
     // groups <= n/kDT + (number of non-empty rows); threads beyond the device-side total exit at once
     long long rows_bound = e->max_cells < kMaxRows ? e->max_cells : kMaxRows;
@@ -260,6 +276,7 @@ int run_sphere_collision(sphb_engine* e) {
     int2* list = e->contacts.p;
     int2* sorted = e->contacts.p + e->posm[cur].cap;
     CK(cudaMemsetAsync(sphere_count_ptr(e), 0, sizeof(int), e->stream));
+    if (int rco = ensure_oid(e)) return rco;
     LAUNCH(e, k_sphere_detect, cdiv(n, 256), 256, 0, e->posm[cur].p, e->oid[cur].p, n, e->d_spheres, e->nspheres, list, sphere_count_ptr(e));
     LAUNCH(e, k_sphere_rank, 148 * 4, 256, 0, list, sphere_count_ptr(e), sorted);
     LAUNCH(e, k_sphere_serial, 1, 32, 0, e->posm[cur].p, e->vel[cur].p, sorted, sphere_count_ptr(e), e->d_spheres, e->nspheres);
@@ -428,6 +445,8 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    e->n_dead = 0;
+    e->oid_identity = false;
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
@@ -457,6 +476,8 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    e->n_dead = 0;
+    e->oid_identity = false;
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
@@ -482,6 +503,7 @@ int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, 
         e->aos_valid = true;
     }
     const int cur = e->cur;
+    if (int rco = ensure_oid(e)) return rco;
     LAUNCH(e, k_invert_perm, cdiv(e->n, 256), 256, 0, e->oid[cur].p, e->inv.p, (int)e->n);
     LAUNCH(e, k_soa_to_aos, cdiv(n, kAosThreads), kAosThreads, kAosThreads * stride, e->aos.p, (int)sw, (int)n, e->inv.p, e->posm[cur].p,
            e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, field_mask);
@@ -499,6 +521,7 @@ int sphb_download_positions(sphb_engine* e, float* xyz, size_t n) {
     if (n == 0) return SPHB_OK;
     const int cur = e->cur;
     CK(e->scratch.reserve(3 * n));
+    if (int rco = ensure_oid(e)) return rco;
     LAUNCH(e, k_invert_perm, cdiv(e->n, 256), 256, 0, e->oid[cur].p, e->inv.p, (int)e->n);
     LAUNCH(e, k_positions_packed, cdiv(n, 256), 256, 0, e->posm[cur].p, e->inv.p, e->scratch.p, (int)n);
     CK(cudaGetLastError());
@@ -564,6 +587,7 @@ int sphb_render_depth(sphb_engine* e, const sphb_camera* cam, float* image) {
     float* d_img = e->scratch.p + npix;
     CK(cudaMemsetAsync(winner, 0, npix * sizeof(unsigned int), e->stream));
     if (n) {
+        if (int rco = ensure_oid(e)) return rco;
         LAUNCH(e, k_invert_perm, cdiv(n, 256), 256, 0, e->oid[cur].p, e->inv.p, n);
         LAUNCH(e, k_splat_winner, cdiv((long long)n * 32, 256), 256, 0, c, e->posm[cur].p, e->inv.p, n, winner);
     }
@@ -643,7 +667,6 @@ int sphb_step(sphb_engine* e, int nsteps) {
     if (rc) return rc;
     if (nsteps < 0) return fail(SPHB_ERR_INVALID, "nsteps < 0");
     if (e->n == 0) return SPHB_OK;
-    const int n = (int)e->n;
     const bool bbox = !e->c.domain_fixed;
     const bool acc = e->params.write_accel != 0;
     if (e->params.laplacian_viscosity) { // optional extra force pass: run the phases one by one
@@ -658,6 +681,8 @@ int sphb_step(sphb_engine* e, int nsteps) {
         if (timed) CK(cudaEventRecord(ev[0], e->stream));
         // Always re-sort: positions moved.  (First step after an upload of an already valid grid is rare.)
         if ((rc = run_sort(e, false))) return rc;
+        const int n = (int)e->n; // after the sort: records marked dead by the slab exchange are gone
+        if (n == 0) return SPHB_OK;
         if (timed) CK(cudaEventRecord(ev[1], e->stream));
         if ((rc = run_density(e, true))) return rc;
         if (timed) CK(cudaEventRecord(ev[2], e->stream));
@@ -753,6 +778,7 @@ int sphb_get_cells(sphb_engine* e, int32_t* cell_xyz, int32_t* perm, int32_t* di
     CK(cudaMemcpyAsync(&g, e->d_grid, sizeof g, cudaMemcpyDeviceToHost, e->stream));
     if (cell_xyz && n) {
         CK(e->scratch.reserve(3 * n));
+        if (int rco = ensure_oid(e)) return rco;
         LAUNCH(e, k_cells_xyz, cdiv(n, 256), 256, 0, e->d_grid, e->posm[e->cur].p, e->oid[e->cur].p, (int*)e->scratch.p, (int)n);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(cell_xyz, e->scratch.p, 3 * n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
@@ -849,6 +875,7 @@ int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, v
     if (vel) *vel = e->vel[cur].p;
     if (aux) *aux = e->aux[cur].p;
     if (accel) *accel = e->accel[cur].p;
+    if (int rco = ensure_oid(e)) return rco;
     if (ids) *ids = e->oid[cur].p;
     return SPHB_OK;
 }
@@ -863,6 +890,7 @@ int sphb_download_soa(sphb_engine* e, float* posm, float* vel, float* aux, float
         if (vel) CK(cudaMemcpyAsync(vel, e->vel[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
         if (aux) CK(cudaMemcpyAsync(aux, e->aux[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
         if (accel) CK(cudaMemcpyAsync(accel, e->accel[cur].p, n * sizeof(float4), cudaMemcpyDeviceToHost, e->stream));
+        if (int rco = ensure_oid(e)) return rco;
         if (ids) CK(cudaMemcpyAsync(ids, e->oid[cur].p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     }
     CK(cudaStreamSynchronize(e->stream));
@@ -902,16 +930,17 @@ extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_lef
     s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
     s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
     s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
-    const int n = (int)e->n, cur = e->cur, nxt = cur ^ 1;
-    const int nb = n ? cdiv(n, kMgThreads) : 1;
-    CK(e->mg_counts.reserve((size_t)3 * nb + 16));
+    const int n = (int)e->n, cur = e->cur;
+    const int nb = n ? cdiv(n, kMgTile) : 1;
+    CK(e->mg_counts.reserve((size_t)kMgStreams * nb + 16 + 2 * (size_t)nb)); // counts, totals + received counts, one byte per warp
     e->mg_blocks = nb;
-    int* totals = e->mg_counts.p + 3 * nb;
-    LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p);
-    LAUNCH(e, k_mg_scan, 3, kMgScanThreads, 0, e->mg_counts.p, nb, totals);
-    const int out_cap = (int)(e->posm[nxt].cap < 0x7fffffffu ? e->posm[nxt].cap : 0x7fffffffu);
-    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, e->posm[nxt].p,
-           e->vel[nxt].p, out_cap, (float4*)msg_left, (float4*)msg_right, (int)capacity);
+    int* totals = e->mg_counts.p + kMgStreams * nb;
+    unsigned char* touch = (unsigned char*)(totals + 16);
+    LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, touch);
+    LAUNCH(e, k_mg_scan, kMgStreams, kMgScanThreads, 0, e->mg_counts.p, nb, n, totals);
+    const int out_cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
+    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, out_cap, touch,
+           (float4*)msg_left, (float4*)msg_right, (int)capacity);
     CK(cudaGetLastError());
     e->mg_pending = true;
     return SPHB_OK;
@@ -928,27 +957,25 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
     s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
     s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
-    const int nxt = e->cur ^ 1;
-    int* totals = e->mg_counts.p + 3 * e->mg_blocks;
+    const int cur = e->cur; // the kept particles stayed in place: everything is appended behind them
+    int* totals = e->mg_counts.p + kMgStreams * e->mg_blocks;
     int* recv = totals + 4;
-    const int cap = (int)(e->posm[nxt].cap < 0x7fffffffu ? e->posm[nxt].cap : 0x7fffffffu);
+    const int cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
     CK(cudaMemsetAsync(recv, 0, 4 * sizeof(int), e->stream));
-    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[nxt].p, e->vel[nxt].p, cap, recv);
-    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[nxt].p, e->vel[nxt].p, cap, recv);
+    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, cap, recv);
+    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, cap, recv);
     CK(cudaGetLastError());
     int h[8];
     CK(cudaMemcpyAsync(h, totals, 8 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    // h[0] = records present before the messages (old count + periodic images, the dead among them included), h[3] = dead
     const long long kept = h[0], cl = h[4], cr = h[5], total = kept + cl + cr;
     e->mg_pending = false;
+    e->n_dead = (size_t)h[3]; // marked in place by the pack, whatever happens below
     if (h[6] > cl || h[7] > cr) return fail(SPHB_ERR_CAPACITY, "a neighbour overflowed its message (wanted %d / %d records)", h[6], h[7]);
     if (total > cap) return fail(SPHB_ERR_CAPACITY, "%lld particles exceed the reserved %d: call sphb_reserve with more room", total, cap);
-    e->cur = nxt;
     e->n = (size_t)total;
-    if (total) {
-        LAUNCH(e, k_fill_iota, cdiv(total, 256), 256, 0, e->oid[nxt].p, (int)total);
-        CK(cudaGetLastError());
-    }
+    e->oid_identity = true; // ids restart at the slot numbers; the next sort reads them as such without an array
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;

@@ -101,6 +101,7 @@ __device__ __forceinline__ void derive_grid(const Consts& c, const BBoxAcc* acc,
         g.dims[a] = (g.dims[a] + 1) / 2;
     }
     g.ncell = g.dims[0] * g.dims[1] * g.dims[2];
+    g.nbins = g.ncell + kTrashBins;
     g.stencil = (c.cell >= c.h2) ? 1 : 2;
     g.stencil_x = c.stencil_x;
 }
@@ -109,7 +110,7 @@ __global__ void __launch_bounds__(256) k_grid_setup(Consts c, const BBoxAcc* acc
     GridDesc g;
     derive_grid(c, acc, g);
     if (blockIdx.x == 0 && threadIdx.x == 0) *out = g;
-    const int total = g.ncell + 1;
+    const int total = g.nbins + 1;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) cell_count[i] = 0;
 }
 
@@ -126,7 +127,7 @@ __device__ __forceinline__ int cell_key(const GridDesc& g, float x, float y, flo
 
 __global__ void __launch_bounds__(256) k_key_hist(const GridDesc* __restrict__ gd, const float4* __restrict__ posm, int n,
                                                   int* __restrict__ key, int* __restrict__ slot, int* __restrict__ cell_count,
-                                                  BBoxAcc* acc, int rearm_bbox) {
+                                                  BBoxAcc* acc, int rearm_bbox, int trash) {
     const GridDesc g = *gd;
     if (rearm_bbox && blockIdx.x == 0 && threadIdx.x < 3) {
         acc->lo[threadIdx.x] = f2ord(INFINITY);
@@ -137,6 +138,7 @@ __global__ void __launch_bounds__(256) k_key_hist(const GridDesc* __restrict__ g
     float4 p = ldg4(posm + i);
     int cx, cy, cz;
     int k = cell_key(g, p.x, p.y, p.z, cx, cy, cz);
+    if (trash && p.w < 0.0f) k = g.ncell + (i & (kTrashBins - 1)); // marked dead by sphb_mg_pack: filed behind the last cell
     key[i] = k;
     slot[i] = atomicAdd(cell_count + k, 1);
 }
@@ -178,7 +180,7 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* total) {
 }
 
 __global__ void __launch_bounds__(kScanThreads) k_scan_reduce(const GridDesc* __restrict__ gd, const int* __restrict__ data, int* __restrict__ block_sums) {
-    const int total = gd->ncell + 1;
+    const int total = gd->nbins + 1;
     const int base = blockIdx.x * kScanTile;
     if (base >= total) return;
     int s = 0;
@@ -194,7 +196,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_reduce(const GridDesc* __
 
 // one block: exclusive scan of the per-tile sums, in place
 __global__ void __launch_bounds__(kScanThreads) k_scan_top(const GridDesc* __restrict__ gd, int* __restrict__ block_sums) {
-    const int ntile = (gd->ncell + 1 + kScanTile - 1) / kScanTile;
+    const int ntile = (gd->nbins + 1 + kScanTile - 1) / kScanTile;
     int carry = 0;
     for (int base = 0; base < ntile; base += kScanThreads) {
         int i = base + threadIdx.x;
@@ -207,7 +209,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_top(const GridDesc* __res
 }
 
 __global__ void __launch_bounds__(kScanThreads) k_scan_apply(const GridDesc* __restrict__ gd, int* __restrict__ data, const int* __restrict__ block_sums) {
-    const int total = gd->ncell + 1;
+    const int total = gd->nbins + 1;
     const int base = blockIdx.x * kScanTile;
     if (base >= total) return;
     // each thread owns kScanPerThread consecutive ints

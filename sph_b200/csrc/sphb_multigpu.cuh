@@ -12,10 +12,14 @@ namespace sphb {
 //   keep       x in [lo - halo, hi + halo): stays in this rank's arrays, owned if x in [lo, hi) else ghost
 //   to left    x <  lo + halo  (owned boundary layer of the left neighbour's ghost zone, and migrants)
 //   to right   x >= hi - halo
-// Ghosts of the previous step (vel.w == 0) are dropped: they are re-sent every step.  All three outputs are
-// compacted in input order with a two-level scan (per-block counts -> scan -> write), so the result is
-// deterministic.  A message is a header record {count, capacity, 0...} followed by 32-byte particle
-// records {posm float4, vel float4}; the receiver appends them and sets the ownership flag itself.
+// Ghosts of the previous step (vel.w == 0) are dropped: they are re-sent every step.  Kept particles STAY WHERE THEY
+// ARE (only a changed ownership flag or a wrapped coordinate is written back); dropped ones are marked dead (mass
+// -1, flag 0) and leave the arrays in the next step's counting sort, which files them behind the last cell
+// (kTrashBins) -- no compaction pass over the state.  The records that do move -- the two messages and the periodic
+// y/z images appended behind the current particles -- are compacted in input order with a two-level scan
+// (per-block counts -> scan -> write), so the result is deterministic.  A message is a header record {count,
+// capacity, 0...} followed by 32-byte particle records {posm float4, vel float4}; the receiver appends them and
+// sets the ownership flag itself.
 
 struct Slab {
     float lo, hi, halo;
@@ -25,7 +29,9 @@ struct Slab {
     float ylo, ylen, zlo, zlen;
 };
 
-constexpr int kMgThreads = 256; // == kScanThreads: block_exclusive_scan is reused
+constexpr int kMgThreads = 256;
+constexpr int kMgPer = 4;                      // consecutive particles per thread (more loads in flight, a quarter of the barriers)
+constexpr int kMgTile = kMgThreads * kMgPer;   // particles per block
 
 // Periodic y / z are handled HERE and nowhere else: an owned particle is wrapped back into the box, and if it lies
 // within `halo` of a periodic face it is emitted once more per face (and once for the edge) shifted by the period,
@@ -35,6 +41,8 @@ struct MgItem {
     int nimg;         // 1, 2 or 4 records: (0,0), (dy,0), (0,dz), (dy,dz)
     float dy, dz;     // image shifts (0 if not near that face)
     bool keep, left, right;
+    bool dies;        // alive so far and not kept: to be marked dead
+    bool dead;        // dead after this pack (dies, or marked by an earlier pack)
 };
 
 __device__ __forceinline__ float mg_wrap(float x, float lo, float len) {
@@ -44,7 +52,8 @@ __device__ __forceinline__ float mg_wrap(float x, float lo, float len) {
 
 __device__ __forceinline__ MgItem mg_classify(const Slab& s, float4 p, const float4& v) {
     MgItem it;
-    const bool owned = v.w != 0.0f;
+    const bool alive = !(p.w < 0.0f);      // not already marked dead by an earlier pack
+    const bool owned = alive && v.w != 0.0f;
     it.dy = it.dz = 0.0f;
     if (s.per_y) {
         p.y = mg_wrap(p.y, s.ylo, s.ylen);
@@ -61,6 +70,8 @@ __device__ __forceinline__ MgItem mg_classify(const Slab& s, float4 p, const flo
     it.keep = owned && x >= s.lo - s.halo && x < s.hi + s.halo;
     it.left = owned && s.has_left && x < s.lo + s.halo;
     it.right = owned && s.has_right && x >= s.hi - s.halo;
+    it.dies = alive && !it.keep;
+    it.dead = !it.keep;
     return it;
 }
 
@@ -76,31 +87,84 @@ __device__ __forceinline__ bool mg_inside(const Slab& s, const float4& p) {
            (!s.per_z || (p.z >= s.zlo && p.z < s.zlo + s.zlen));
 }
 
-// pass 1: per-block record counts of (keep, left, right)
+// The four record counts of a thread (each <= 4 per particle, block sums <= 4096) travel as 16-bit fields of one 64-bit word, so
+// one block scan serves all four streams (the first version ran one 32-bit block scan per stream: k_mg_count and
+// k_mg_write were bound by those barriers, not by memory).
+constexpr int kMgStreams = 4; // periodic images of kept particles, to left, to right, dead
+
+__device__ __forceinline__ unsigned long long mg_pack4(int a, int b, int c, int d) {
+    return (unsigned long long)a | ((unsigned long long)b << 16) | ((unsigned long long)c << 32) | ((unsigned long long)d << 48);
+}
+__device__ __forceinline__ int mg_field(unsigned long long v, int k) { return (int)((v >> (16 * k)) & 0xffffull); }
+
+// exclusive prefix of v over the block of kMgThreads threads; *total = block sum.  Two barriers.
+__device__ __forceinline__ unsigned long long mg_block_scan(unsigned long long v, unsigned long long* total) {
+    __shared__ unsigned long long s_warp[kMgThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    unsigned long long off = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kMgThreads / 32; w++) { // 8 warps: every thread sums the broadcast partials itself
+        const unsigned long long x = s_warp[w];
+        if (w < warp) off += x;
+        tot += x;
+    }
+    *total = tot;
+    return off + inc - v;
+}
+
+// pass 1: per-block record counts, one array per stream: block_counts[k * nblocks + block]
 __global__ void __launch_bounds__(kMgThreads) k_mg_count(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
-                                                         int* __restrict__ block_counts) {
-    const int i = blockIdx.x * kMgThreads + threadIdx.x;
-    int c[3] = {0, 0, 0};
-    if (i < n) {
-        const MgItem it = mg_classify(s, posm[i], vel[i]);
-        c[0] = it.keep ? it.nimg : 0;
-        c[1] = it.left ? it.nimg : 0;
-        c[2] = it.right ? it.nimg : 0;
+                                                         int* __restrict__ block_counts, unsigned char* __restrict__ touch) {
+    const int i0 = blockIdx.x * kMgTile + threadIdx.x * kMgPer;
+    unsigned long long c = 0;
+    bool work = false; // something for pass 3 to do here: records to emit, a flag / wrap to write back, a particle to mark dead
+    float4 p[kMgPer], v[kMgPer];
+#pragma unroll
+    for (int q = 0; q < kMgPer; q++) {
+        const int i = max(min(i0 + q, n - 1), 0);
+        p[q] = ldg4(posm + i);
+        v[q] = ldg4(vel + i);
     }
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-        int tot;
-        block_exclusive_scan(c[k], &tot);
-        if (threadIdx.x == 0) block_counts[3 * blockIdx.x + k] = tot;
+    for (int q = 0; q < kMgPer; q++) {
+        if (i0 + q >= n) break;
+        const MgItem it = mg_classify(s, p[q], v[q]);
+        c += mg_pack4(it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0, it.dead ? 1 : 0);
+        work |= it.left || it.right || it.dies ||
+                (it.keep && (it.nimg > 1 || it.p.y != p[q].y || it.p.z != p[q].z || (mg_inside(s, it.p) ? 1.0f : 0.0f) != v[q].w));
+    }
+    // one byte per warp (128 consecutive particles): pass 3 skips the warps with nothing to do -- away from the slab
+    // faces that is most of them -- without reading their particles again
+    const bool any = __any_sync(0xffffffffu, work);
+    if ((threadIdx.x & 31) == 0) touch[blockIdx.x * (kMgThreads / 32) + (threadIdx.x >> 5)] = any ? 1 : 0;
+    // block sum only: warp reduction, then one shared-memory round
+    __shared__ unsigned long long s_part[kMgThreads / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x < kMgStreams) {
+        unsigned long long tot = 0;
+#pragma unroll
+        for (int w = 0; w < kMgThreads / 32; w++) tot += s_part[w];
+        block_counts[threadIdx.x * gridDim.x + blockIdx.x] = mg_field(tot, threadIdx.x);
     }
 }
 
 // pass 2: the per-block counts become exclusive offsets (and totals).  One block of 1024 threads per stream
-// (keep / left / right), four entries per thread per round: 70 K blocks take 18 rounds (the first version, one
+// (images / left / right / dead), four entries per thread per round: 70 K blocks take 18 rounds (the first version, one
 // 256-thread block for all three streams, took 0.34 ms of a 7.4 ms step at 17.8 M particles).
 constexpr int kMgScanThreads = 1024;
 
-__global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int* __restrict__ totals) {
+__global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int n, int* __restrict__ totals) {
     __shared__ int s_warp[kMgScanThreads / 32];
     const int k = blockIdx.x; // stream
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -111,7 +175,7 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
         int tsum = 0;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            v[q] = (b0 + q < nblocks) ? block_counts[3 * (b0 + q) + k] : 0;
+            v[q] = (b0 + q < nblocks) ? block_counts[k * nblocks + b0 + q] : 0;
             tsum += v[q];
         }
         int inc = tsum;
@@ -136,52 +200,86 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
         const int round_total = s_warp[kMgScanThreads / 32 - 1];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            if (b0 + q < nblocks) block_counts[3 * (b0 + q) + k] = ex;
+            if (b0 + q < nblocks) block_counts[k * nblocks + b0 + q] = ex;
             ex += v[q];
         }
         carry += round_total;
         __syncthreads(); // s_warp is reused next round
     }
-    if (threadIdx.x == 0) totals[k] = carry;
+    // totals: [0] = records in the arrays after the local images are appended (where received records go),
+    // [1], [2] = message sizes, [3] = dead records among the first n
+    if (threadIdx.x == 0) totals[k] = k == 0 ? carry + n : carry;
 }
 
-// pass 3: write.  keep -> (posm_out, vel_out) with the ownership flag refreshed; left/right -> messages.
-__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
+// pass 3: write.  A kept particle stays in its slot (flag refreshed, wrapped coordinates written back); its periodic
+// images go behind the current particles (slot n + offset); a dropped one is marked dead; left/right -> messages.
+// posm/vel are read and written by the thread that owns slot i only.
+__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restrict__ posm, float4* __restrict__ vel, int n,
                                                          const int* __restrict__ block_offsets, const int* __restrict__ totals,
-                                                         float4* __restrict__ posm_out, float4* __restrict__ vel_out, int out_capacity,
+                                                         int out_capacity, const unsigned char* __restrict__ touch,
                                                          float4* __restrict__ msg_left, float4* __restrict__ msg_right, int capacity) {
-    const int i = blockIdx.x * kMgThreads + threadIdx.x;
-    MgItem it;
-    it.keep = it.left = it.right = false;
-    it.nimg = 0;
-    if (i < n) it = mg_classify(s, posm[i], vel[i]);
-    int off[3];
-    const int cnt[3] = {it.keep ? it.nimg : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0};
+    const int i0 = blockIdx.x * kMgTile + threadIdx.x * kMgPer;
+    const bool active = touch[blockIdx.x * (kMgThreads / 32) + (threadIdx.x >> 5)] != 0; // warp-uniform
+    // phase 1: this thread's record counts (nothing is kept in registers: phase 2 reads the four particles again,
+    // from L1 -- holding them cost 107 registers and three quarters of the occupancy)
+    unsigned long long mine = 0;
+    if (active) {
+        float4 pp[kMgPer], vv[kMgPer];
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-        int tot;
-        off[k] = block_exclusive_scan(cnt[k], &tot) + block_offsets[3 * blockIdx.x + k];
+        for (int q = 0; q < kMgPer; q++) {
+            const int i = max(min(i0 + q, n - 1), 0);
+            pp[q] = posm[i];
+            vv[q] = vel[i];
+        }
+#pragma unroll
+        for (int q = 0; q < kMgPer; q++) {
+            if (i0 + q >= n) break;
+            const MgItem it = mg_classify(s, pp[q], vv[q]);
+            mine += mg_pack4(it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0, 0);
+        }
     }
-    for (int img = 0; img < cnt[0]; img++) {
-        if (off[0] + img >= out_capacity) break;
-        const float4 q = mg_image(it, img, 0.0f);
-        posm_out[off[0] + img] = q;
-        vel_out[off[0] + img] = make_float4(it.v.x, it.v.y, it.v.z, (img == 0 && mg_inside(s, q)) ? 1.0f : 0.0f);
-    }
-    for (int img = 0; img < cnt[1]; img++) {
-        if (off[1] + img >= capacity) break;
-        float4 q = mg_image(it, img, s.shift_left);
-        // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
-        if (s.shift_left != 0.0f && it.p.x < s.lo) q.x = fminf(q.x, nextafterf(s.lo + s.shift_left, -INFINITY));
-        msg_left[2 + 2 * (off[1] + img)] = q;
-        msg_left[3 + 2 * (off[1] + img)] = it.v;
-    }
-    for (int img = 0; img < cnt[2]; img++) {
-        if (off[2] + img >= capacity) break;
-        float4 q = mg_image(it, img, s.shift_right);
-        if (s.shift_right != 0.0f && it.p.x >= s.hi) q.x = fmaxf(q.x, s.hi + s.shift_right);
-        msg_right[2 + 2 * (off[2] + img)] = q;
-        msg_right[3 + 2 * (off[2] + img)] = it.v;
+    unsigned long long tot;
+    const unsigned long long ex = mg_block_scan(mine, &tot);
+    int off[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) off[k] = mg_field(ex, k) + block_offsets[k * gridDim.x + blockIdx.x];
+#pragma unroll 1
+    for (int q = 0; q < kMgPer; q++) {
+        const int i = i0 + q;
+        if (i >= n || !active) break;
+        const float4 p_q = posm[i];
+        const MgItem it = mg_classify(s, p_q, vel[i]);
+        const int cnt[3] = {it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0};
+        if (it.keep) {
+            const float flag = mg_inside(s, it.p) ? 1.0f : 0.0f;
+            if (flag != it.v.w) vel[i].w = flag;
+            if (it.p.y != p_q.y || it.p.z != p_q.z) posm[i] = it.p; // wrapped into the periodic box
+        } else if (it.dies) {
+            posm[i].w = -1.0f;
+            vel[i].w = 0.0f;
+        }
+        for (int img = 0; img < cnt[0]; img++) {
+            const int dst = n + off[0] + img;
+            if (dst >= out_capacity) break;
+            posm[dst] = mg_image(it, img + 1, 0.0f);
+            vel[dst] = make_float4(it.v.x, it.v.y, it.v.z, 0.0f);
+        }
+        for (int img = 0; img < cnt[1]; img++) {
+            if (off[1] + img >= capacity) break;
+            float4 w = mg_image(it, img, s.shift_left);
+            // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
+            if (s.shift_left != 0.0f && it.p.x < s.lo) w.x = fminf(w.x, nextafterf(s.lo + s.shift_left, -INFINITY));
+            msg_left[2 + 2 * (off[1] + img)] = w;
+            msg_left[3 + 2 * (off[1] + img)] = it.v;
+        }
+        for (int img = 0; img < cnt[2]; img++) {
+            if (off[2] + img >= capacity) break;
+            float4 w = mg_image(it, img, s.shift_right);
+            if (s.shift_right != 0.0f && it.p.x >= s.hi) w.x = fmaxf(w.x, s.hi + s.shift_right);
+            msg_right[2 + 2 * (off[2] + img)] = w;
+            msg_right[3 + 2 * (off[2] + img)] = it.v;
+        }
+        off[0] += cnt[0]; off[1] += cnt[1]; off[2] += cnt[2];
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) { // headers: count, capacity
         if (msg_left) msg_left[0] = make_float4(__int_as_float(s.has_left ? totals[1] : 0), __int_as_float(capacity), 0.0f, 0.0f);

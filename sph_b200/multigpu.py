@@ -186,7 +186,7 @@ def bench_main(args, world, rank, local):
                           write_accel=0 if args.no_accel else 1)
         n_own = len(ps)
         capacity = int((L + 2 * halo) ** 2 * 1100.0 * halo * 1.6) + 4096
-        eng.reserve(int(n_own * ((L + 2 * halo) / L) ** 3 * 1.08) + 2 * capacity)
+        eng.reserve(int(n_own * ((L + 2 * halo) / L) ** 3 * 1.08) * 2 - n_own + 4 * capacity)   # old ghosts stay (dead) until the next sort
         what = f", periodic box {L:.1f}^3 per GPU ({world} side by side in x), gravity off, no walls"
     else:
         scale = {"drop16m": 1, "drop2m": 2, "drop256k": 4}.get(args.workload)
@@ -215,7 +215,7 @@ def bench_main(args, world, rank, local):
         column = (192 + (256 if strong else 0)) // scale * 0.1 + 0.5        # a strong-scaling cut may pass through the falling block
         face = (section + 0.2) * column * 1100.0                             # particles per unit x near a face (upper bound)
         capacity = int(face * halo * 2.0) + 4096
-        eng.reserve(n_own + 2 * capacity)
+        eng.reserve(n_own + 4 * capacity)   # last step's ghosts stay (marked dead) until the next sort drops them
         what = (f", ONE tank cut into {world} x-slabs at particle-count quantiles" if strong
                 else f", one tank section per GPU ({world} sections side by side)")
     sr = SlabRank(eng, slab, capacity, local)
@@ -289,6 +289,24 @@ def bench_main(args, world, rank, local):
     assert total == int(expect.item()), f"particles lost or duplicated by the exchange: {total} owned, {int(expect.item())} generated"
     value = total * args.steps / (ms * 1e-3)
 
+    # where the time between two engine steps goes (a few extra steps, events on the engine's stream; not part of `value`)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    parts = np.zeros(3)
+    nb = 4
+    for _ in range(nb):
+        ev[0].record(sr.stream)
+        sr.pack()
+        ev[1].record(sr.stream)
+        sr.exchange_distributed(dist, left, right)
+        ev[2].record(sr.stream)
+        sr.unpack()                      # synchronises (reads the counts)
+        ev[3].record(sr.stream)
+        eng.step(1)
+        since_reset[0] += 1
+        eng.synchronize()
+        parts += [ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])]
+    parts /= nb
+
     # end to end on host records: upload own records, exchange ghosts, step, download own records
     e2e_steps = max(1, args.e2e_steps)
     out = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
@@ -331,7 +349,8 @@ def bench_main(args, world, rank, local):
                          "traffic": None, "peak_source": peak_src, "bytes_per_particle": bforce, "kernel_ms": float(phase[2]),
                          "local_particles_incl_ghosts": n_local, "steps_averaged": int(timed)},
             "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "engine_step": float(phase[3]),
-                         "exchange_and_pack": ms / args.steps - float(phase[3])},
+                         "exchange_and_pack": ms / args.steps - float(phase[3]),
+                         "breakdown_rank0": {"pack": float(parts[0]), "send_recv": float(parts[1]), "unpack": float(parts[2])}},
             "halo": {"counts_rank0": {"kept": sr.counts[0], "from_left": sr.counts[1], "from_right": sr.counts[2]},
                      "message_capacity": capacity},
             "cpu_baseline": None,

@@ -28,7 +28,7 @@ def run_slabs(ps, walls, steps, world, bounds, halo):
         own = ps[(ps["pos"][:, 0] >= slab.lo) & (ps["pos"][:, 0] < slab.hi)].copy()
         e = sph_b200.Engine()
         e.set_walls(walls)
-        e.reserve(len(ps))
+        e.reserve(2 * len(ps))          # own + last step's ghosts (dead until the next sort) + the new ones
         e.upload(own)
         ranks.append(multigpu.SlabRank(e, slab, capacity=len(ps), device_index=0))
     history = []
@@ -96,7 +96,7 @@ def test_message_overflow_is_reported():
     for r in range(2):
         slab = multigpu.make_slab(r, 2, bounds, 2 * R)
         e = sph_b200.Engine()
-        e.reserve(len(ps))
+        e.reserve(2 * len(ps))
         e.upload(ps[(x >= slab.lo) & (x < slab.hi)].copy())
         ranks.append(multigpu.SlabRank(e, slab, capacity=8, device_index=0))     # far too small
     for r in ranks:
@@ -151,7 +151,7 @@ def test_periodic_box_matches_reference_arithmetic_on_images(oracle, world):
         slab = multigpu.make_slab(r, world, bounds, halo, period=float(L), yz_box=((0.0, float(L)), (0.0, float(L))))
         own = ps[(ps["pos"][:, 0] >= slab.lo) & (ps["pos"][:, 0] < slab.hi)].copy()
         e = sph_b200.Engine(gravity=(0.0, 0.0, 0.0))
-        e.reserve(8 * len(ps))
+        e.reserve(12 * len(ps))
         e.upload(own)
         ranks.append(multigpu.SlabRank(e, slab, capacity=4 * len(ps), device_index=0))
     for r in ranks:
@@ -192,7 +192,7 @@ def test_periodic_wrap_and_migration_conserve_particles():
     for r in range(2):
         slab = multigpu.make_slab(r, 2, bounds, halo, period=L, yz_box=((0.0, L), (0.0, L)))
         e = sph_b200.Engine(gravity=(0.0, 0.0, 0.0))
-        e.reserve(6 * len(ps))
+        e.reserve(10 * len(ps))
         e.upload(ps[(ps["pos"][:, 0] >= slab.lo) & (ps["pos"][:, 0] < slab.hi)].copy())
         ranks.append(multigpu.SlabRank(e, slab, capacity=3 * len(ps), device_index=0))
     for step in range(40):
