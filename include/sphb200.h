@@ -261,6 +261,8 @@ int sphb_reserve(sphb_engine* e, size_t n_max);
  * (marked dead in place; a negative mass means "dead" to an engine that has used sphb_mg_pack).
  * Deterministic (order-preserving compaction of the messages).  Asynchronous on the engine's stream. */
 int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* msg_right, size_t capacity);
+/* The same with a capacity per message (see sphb_mg_sent). */
+int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* msg_left, size_t cap_left, void* msg_right, size_t cap_right);
 
 /* Append what the neighbours sent (NULL = none), refresh the ownership flags and adopt the new particle
  * set.  Synchronises once to read the counts.  counts[4] (may be NULL) = {records before the messages (the dropped
@@ -268,6 +270,12 @@ int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* ms
  * them), from_left, from_right, total}.  sphb_count() excludes the dead again after the next step.
  * SPHB_ERR_CAPACITY if a sender overflowed its message or the arrays reserved with sphb_reserve are full. */
 int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, size_t counts[4]);
+
+/* Records the last sphb_mg_pack wanted to put into its left / right message (known once sphb_mg_unpack has read the
+ * counts back).  Both ends of a link see the same number -- the sender here, the receiver in counts[1] / counts[2] --
+ * so they can agree, without talking, to transfer only a prefix of the message buffers next step (pass the smaller
+ * capacity to sphb_mg_pack; sph_b200/multigpu.py does). */
+int sphb_mg_sent(sphb_engine* e, size_t sent[2]);
 
 /* --- allocation-free bounding box ------------------------------------------------------------------ */
 

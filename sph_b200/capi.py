@@ -69,7 +69,7 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_unpack",
+    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent",
 ]
 
 _lib = None
@@ -134,6 +134,8 @@ def load_library() -> C.CDLL:
     L.sphb_reserve.argtypes = [vp, sz]
     L.sphb_mg_pack.argtypes = [vp, C.POINTER(Slab), vp, vp, sz]
     L.sphb_mg_unpack.argtypes = [vp, C.POINTER(Slab), vp, vp, C.POINTER(sz * 4)]
+    L.sphb_mg_sent.argtypes = [vp, C.POINTER(sz * 2)]
+    L.sphb_mg_pack_limits.argtypes = [vp, C.POINTER(Slab), vp, sz, vp, sz]
     _lib = L
     return L
 
@@ -274,11 +276,20 @@ class Engine:
         self._check(self.lib.sphb_mg_pack(self.h, C.byref(slab), C.c_void_p(msg_left) if msg_left else None,
                                           C.c_void_p(msg_right) if msg_right else None, capacity))
 
+    def mg_pack_limits(self, slab: Slab, msg_left: int | None, cap_left: int, msg_right: int | None, cap_right: int):
+        self._check(self.lib.sphb_mg_pack_limits(self.h, C.byref(slab), C.c_void_p(msg_left) if msg_left else None, cap_left,
+                                                 C.c_void_p(msg_right) if msg_right else None, cap_right))
+
     def mg_unpack(self, slab: Slab, from_left: int | None, from_right: int | None):
         counts = (C.c_size_t * 4)()
         self._check(self.lib.sphb_mg_unpack(self.h, C.byref(slab), C.c_void_p(from_left) if from_left else None,
                                             C.c_void_p(from_right) if from_right else None, C.byref(counts)))
         return tuple(int(c) for c in counts)
+
+    def mg_sent(self):
+        sent = (C.c_size_t * 2)()
+        self._check(self.lib.sphb_mg_sent(self.h, C.byref(sent)))
+        return int(sent[0]), int(sent[1])
 
     # --- the SphUtils methods
     def update_cells(self):

@@ -81,6 +81,7 @@ struct sphb_engine {
     DevBuf<int2> contacts;  // particle-sphere contacts: (original id, slot), unsorted then sorted (2 x capacity)
     DevBuf<int> mg_counts;  // multi-GPU pack: 3 per block, then totals[3] and recv_counts[4]
     int mg_blocks = 0;
+    size_t mg_sent[2] = {0, 0}; // records the last pack put (wanted to put) into its left / right message, known after unpack
     bool mg_pending = false; // sphb_mg_pack ran, sphb_mg_unpack has not committed yet
     size_t reserved = 0;
     GridDesc* d_grid = nullptr;
@@ -917,11 +918,15 @@ extern "C" int sphb_reserve(sphb_engine* e, size_t n_max) {
 }
 
 extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* msg_right, size_t capacity) {
+    return sphb_mg_pack_limits(e, slab, msg_left, capacity, msg_right, capacity);
+}
+
+extern "C" int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* msg_left, size_t cap_left, void* msg_right, size_t cap_right) {
     int rc = check_ready(e);
     if (rc) return rc;
     if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
     if ((slab->has_left && !msg_left) || (slab->has_right && !msg_right)) return fail(SPHB_ERR_INVALID, "missing message buffer");
-    if (capacity > 0x3fffffffu) return fail(SPHB_ERR_CAPACITY, "message capacity too large");
+    if (cap_left > 0x3fffffffu || cap_right > 0x3fffffffu) return fail(SPHB_ERR_CAPACITY, "message capacity too large");
     if ((slab->periodic_y && !(slab->ylen >= 2.0f * slab->halo)) || (slab->periodic_z && !(slab->zlen >= 2.0f * slab->halo)))
         return fail(SPHB_ERR_INVALID, "a periodic axis must be at least two halos long");
     Slab s;
@@ -940,9 +945,16 @@ extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_lef
     LAUNCH(e, k_mg_scan, kMgStreams, kMgScanThreads, 0, e->mg_counts.p, nb, n, totals);
     const int out_cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
     LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, out_cap, touch,
-           (float4*)msg_left, (float4*)msg_right, (int)capacity);
+           (float4*)msg_left, (float4*)msg_right, (int)cap_left, (int)cap_right);
     CK(cudaGetLastError());
     e->mg_pending = true;
+    return SPHB_OK;
+}
+
+extern "C" int sphb_mg_sent(sphb_engine* e, size_t sent[2]) {
+    if (!e || !sent) return fail(SPHB_ERR_INVALID, "null argument");
+    sent[0] = e->mg_sent[0];
+    sent[1] = e->mg_sent[1];
     return SPHB_OK;
 }
 
@@ -972,6 +984,8 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     const long long kept = h[0], cl = h[4], cr = h[5], total = kept + cl + cr;
     e->mg_pending = false;
     e->n_dead = (size_t)h[3]; // marked in place by the pack, whatever happens below
+    e->mg_sent[0] = (size_t)h[1];
+    e->mg_sent[1] = (size_t)h[2];
     if (h[6] > cl || h[7] > cr) return fail(SPHB_ERR_CAPACITY, "a neighbour overflowed its message (wanted %d / %d records)", h[6], h[7]);
     if (total > cap) return fail(SPHB_ERR_CAPACITY, "%lld particles exceed the reserved %d: call sphb_reserve with more room", total, cap);
     e->n = (size_t)total;

@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
 __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restrict__ posm, float4* __restrict__ vel, int n,
                                                          const int* __restrict__ block_offsets, const int* __restrict__ totals,
                                                          int out_capacity, const unsigned char* __restrict__ touch,
-                                                         float4* __restrict__ msg_left, float4* __restrict__ msg_right, int capacity) {
+                                                         float4* __restrict__ msg_left, float4* __restrict__ msg_right, int cap_left, int cap_right) {
     const int i0 = blockIdx.x * kMgTile + threadIdx.x * kMgPer;
     const bool active = touch[blockIdx.x * (kMgThreads / 32) + (threadIdx.x >> 5)] != 0; // warp-uniform
     // phase 1: this thread's record counts (nothing is kept in registers: phase 2 reads the four particles again,
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
             vel[dst] = make_float4(it.v.x, it.v.y, it.v.z, 0.0f);
         }
         for (int img = 0; img < cnt[1]; img++) {
-            if (off[1] + img >= capacity) break;
+            if (off[1] + img >= cap_left) break;
             float4 w = mg_image(it, img, s.shift_left);
             // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
             if (s.shift_left != 0.0f && it.p.x < s.lo) w.x = fminf(w.x, nextafterf(s.lo + s.shift_left, -INFINITY));
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
             msg_left[3 + 2 * (off[1] + img)] = it.v;
         }
         for (int img = 0; img < cnt[2]; img++) {
-            if (off[2] + img >= capacity) break;
+            if (off[2] + img >= cap_right) break;
             float4 w = mg_image(it, img, s.shift_right);
             if (s.shift_right != 0.0f && it.p.x >= s.hi) w.x = fmaxf(w.x, s.hi + s.shift_right);
             msg_right[2 + 2 * (off[2] + img)] = w;
@@ -282,8 +282,8 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
         off[0] += cnt[0]; off[1] += cnt[1]; off[2] += cnt[2];
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) { // headers: count, capacity
-        if (msg_left) msg_left[0] = make_float4(__int_as_float(s.has_left ? totals[1] : 0), __int_as_float(capacity), 0.0f, 0.0f);
-        if (msg_right) msg_right[0] = make_float4(__int_as_float(s.has_right ? totals[2] : 0), __int_as_float(capacity), 0.0f, 0.0f);
+        if (msg_left) msg_left[0] = make_float4(__int_as_float(s.has_left ? totals[1] : 0), __int_as_float(cap_left), 0.0f, 0.0f);
+        if (msg_right) msg_right[0] = make_float4(__int_as_float(s.has_right ? totals[2] : 0), __int_as_float(cap_right), 0.0f, 0.0f);
     }
 }
 

@@ -64,10 +64,14 @@ def quantile_bounds(x: np.ndarray, world: int, cell: float, lo: float, hi: float
     return [lo] + inner + [hi]
 
 
-def exchange(dist, send_left, send_right, recv_left, recv_right, left, right):
+def exchange(dist, send_left, send_right, recv_left, recv_right, left, right, nbytes=None):
     """Post the (at most) four point-to-point operations of one halo exchange and wait for them.
     Works on any backend (NCCL on device tensors, gloo on CPU tensors in the tests).  A rank that is its own
-    neighbour (one rank, periodic x) copies locally."""
+    neighbour (one rank, periodic x) copies locally.  nbytes = (out_left, out_right, in_left, in_right): transfer
+    only these prefixes of the buffers (both ends of a link must pass the same number, see SlabRank)."""
+    if nbytes is not None:
+        send_left, send_right = send_left[:nbytes[0]], send_right[:nbytes[1]]
+        recv_left, recv_right = recv_left[:nbytes[2]], recv_right[:nbytes[3]]
     me = dist.get_rank() if dist is not None and dist.is_initialized() else 0
     if left == me and right == me:       # world size 1, periodic x
         recv_left.copy_(send_right)
@@ -103,22 +107,37 @@ class SlabRank:
         self.send_left, self.send_right, self.recv_left, self.recv_right = mk(), mk(), mk(), mk()
         self.stream = torch.cuda.ExternalStream(engine.stream(), device=dev)
         self.counts = (0, 0, 0, 0)
+        # Records each of the four messages may carry in the NEXT exchange.  The buffers are sized for the worst case
+        # (capacity), but sending them whole every step costs more than the step's compute once slabs get thin
+        # (8-way strong scaling: 2 x 33 MB per rank and step).  Both ends of a link know how many records the last
+        # message held -- the sender from sphb_mg_sent, the receiver from the unpack counts -- so both apply the same
+        # rule to that number and agree on the size without talking: 1.5 x last + 4096, at most the capacity.
+        # Counts drift by well under a per cent per step; a message that would not fit is reported by unpack.
+        self.adaptive = True
+        self.out_left = self.out_right = self.in_left = self.in_right = self.capacity
+
+    def _limit(self, last: int) -> int:
+        return min(self.capacity, int(last * 1.5) + 4096) if self.adaptive else self.capacity
 
     def pack(self):
         s = self.slab
-        self.engine.mg_pack(s, self.send_left.data_ptr() if s.has_left else None,
-                            self.send_right.data_ptr() if s.has_right else None, self.capacity)
+        self.engine.mg_pack_limits(s, self.send_left.data_ptr() if s.has_left else None, self.out_left,
+                                   self.send_right.data_ptr() if s.has_right else None, self.out_right)
 
     def unpack(self):
         s = self.slab
         self.counts = self.engine.mg_unpack(s, self.recv_left.data_ptr() if s.has_left else None,
                                             self.recv_right.data_ptr() if s.has_right else None)
+        sent = self.engine.mg_sent()
+        self.out_left, self.out_right = self._limit(sent[0]), self._limit(sent[1])
+        self.in_left, self.in_right = self._limit(self.counts[1]), self._limit(self.counts[2])
         return self.counts
 
     def exchange_distributed(self, dist, left, right):
         # NCCL enqueues after the current stream: make that the engine's stream so pack -> send and recv -> unpack order
+        nbytes = tuple(32 * (k + 1) for k in (self.out_left, self.out_right, self.in_left, self.in_right))
         with self.torch.cuda.stream(self.stream):
-            exchange(dist, self.send_left, self.send_right, self.recv_left, self.recv_right, left, right)
+            exchange(dist, self.send_left, self.send_right, self.recv_left, self.recv_right, left, right, nbytes)
 
     def step(self, dist=None, left=None, right=None):
         self.pack()
@@ -142,10 +161,14 @@ def exchange_in_process(ranks, periodic=False):
         r.engine.synchronize()
     for i, r in enumerate(ranks):
         left, right = neighbours(i, world, periodic)
-        if right is not None:
-            ranks[right].recv_left.copy_(r.send_right)
+        if right is not None:   # only what a real exchange would transfer, and both ends must have agreed on it
+            assert r.out_right == ranks[right].in_left, "the two ends of a link disagree on the message size"
+            nb = 32 * (r.out_right + 1)
+            ranks[right].recv_left[:nb].copy_(r.send_right[:nb])
         if left is not None:
-            ranks[left].recv_right.copy_(r.send_left)
+            assert r.out_left == ranks[left].in_right, "the two ends of a link disagree on the message size"
+            nb = 32 * (r.out_left + 1)
+            ranks[left].recv_right[:nb].copy_(r.send_left[:nb])
     ranks[0].torch.cuda.synchronize()
 
 
