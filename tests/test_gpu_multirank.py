@@ -217,3 +217,47 @@ def test_periodic_wrap_and_migration_conserve_particles():
     assert np.isfinite(allp).all()
     assert np.all((allp[:, :3] >= 0.0) & (allp[:, :3] < np.float32(L) + 1e-6))
     assert 0.9 * 0.033 * 40 > L / 2 / 4                  # the drift really carried particles across slabs and faces
+
+
+def test_dropped_ghosts_stay_dead_until_the_next_sort():
+    """The pack does not compact: last step's ghosts are marked dead (mass -1, flag 0) in their slots, the received
+    records are appended behind them, and the next step's counting sort drops the dead.  Counts before and after,
+    and a download between unpack and step (ids are materialised lazily there) must be consistent."""
+    ps, walls = scenes.dam_break(20, 12, 12)
+    R = multigpu.support_radius()
+    x = ps["pos"][:, 0]
+    bounds = [float(x.min()) - 1, float(np.median(x)), float(x.max()) + 1]
+    ranks = []
+    for r in range(2):
+        slab = multigpu.make_slab(r, 2, bounds, 2 * R * 1.001)
+        e = sph_b200.Engine()
+        e.set_walls(walls)
+        e.reserve(2 * len(ps))
+        e.upload(ps[(x >= slab.lo) & (x < slab.hi)].copy())
+        ranks.append(multigpu.SlabRank(e, slab, capacity=len(ps), device_index=0))
+    n_own = [r.engine.count() for r in ranks]
+    ghosts_prev = [0, 0]
+    for step in range(3):
+        for r in ranks:
+            r.pack()
+        multigpu.exchange_in_process(ranks)
+        for k, r in enumerate(ranks):
+            kept, fl, fr, total = r.unpack()
+            assert total == kept + fl + fr == r.engine.count()
+            assert kept == n_own[k] + ghosts_prev[k]                 # nothing moved: own + last step's ghosts (now dead)
+            posm, velw, _, _, ids = r.engine.download_soa()
+            dead = posm[:, 3] < 0
+            assert dead.sum() == ghosts_prev[k] and not velw[dead, 3].any()
+            assert np.array_equal(ids, np.arange(total))              # ids restart at the slot numbers
+            owned_now = int((velw[:, 3] != 0).sum())
+            ghosts_now = int((~dead & (velw[:, 3] == 0)).sum())      # received, plus own particles that just left the slab
+            assert ghosts_now >= fl + fr
+            r.engine.step(1)
+            assert r.engine.count() == total - ghosts_prev[k]         # the sort dropped the dead
+            posm2 = r.engine.download_soa()[0]
+            assert (posm2[:, 3] > 0).all()
+            ghosts_prev[k] = ghosts_now
+            n_own[k] = owned_now
+    assert sum(n_own) == len(ps)
+    for r in ranks:
+        r.engine.close()
