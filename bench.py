@@ -201,12 +201,15 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="multi-GPU: weak = one 16.7 M-particle tank section per GPU (default); strong = the ONE config-4 tank "
                          "cut into N slabs at particle-count quantiles")
-    ap.add_argument("--reset-every", type=int, default=16,
+    ap.add_argument("--reset-every", type=int, default=None,
                     help="restore the initial state (device-to-device, inside the timed region) every this many steps: the "
-                         "reference's scheme (dt=0.033, k=100) blows up on deep pools after ~35 steps, in its own arithmetic too")
+                         "reference's scheme (dt=0.033, k=100) blows up on deep pools after ~35 steps, in its own arithmetic too "
+                         "(default 16; 8 for the pre-compressed 64 K dam break, which explodes within a dozen steps)")
     ap.add_argument("--cell-frac", type=float, default=1.0, help="grid cell edge as a fraction of the support radius h*h (>= 0.5)")
     ap.add_argument("--cell-x-div", type=int, default=0, help="x pitch of the grid = cell / this (0 = engine default, 2)")
     args = ap.parse_args()
+    if args.reset_every is None:
+        args.reset_every = 8 if args.workload == "dam64k" else 16
     if args.impl == "reference":
         return run_reference_arm(args)
     if args.warmup < 3:

@@ -24,6 +24,14 @@ __global__ void __launch_bounds__(256) k_scatter(const int* __restrict__ key, co
 constexpr int kStableRankLimit = 4096;
 
 template <bool kCarryAll>
+__device__ __forceinline__ void rank_gather_one(int p, const int2* pairs, const int* key, const int* cell_start,
+                                                const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
+                                                const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
+                                                float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                float4* __restrict__ aux_out, float4* __restrict__ acc_out,
+                                                int* __restrict__ oid_out, int ncell);
+
+template <bool kCarryAll>
 __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pairs, const int* __restrict__ key, const int* __restrict__ cell_start,
                                                      const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
                                                      const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
@@ -32,9 +40,19 @@ __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pa
                                                      int* __restrict__ oid_out, int n, const GridDesc* __restrict__ gd) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
+    rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, gd->ncell);
+}
+
+template <bool kCarryAll>
+__device__ __forceinline__ void rank_gather_one(int p, const int2* pairs, const int* key, const int* cell_start,
+                                                const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
+                                                const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
+                                                float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                float4* __restrict__ aux_out, float4* __restrict__ acc_out,
+                                                int* __restrict__ oid_out, int ncell) {
     const int2 me = pairs[p];
     const int k = key[me.y];
-    if (k >= gd->ncell) return; // a trash bin: records the slab exchange marked dead end here and are not carried over
+    if (k >= ncell) return; // a trash bin: records the slab exchange marked dead end here and are not carried over
     const int b = cell_start[k], e = cell_start[k + 1];
     int rank = 0;
     if (e - b <= kStableRankLimit) {
@@ -106,11 +124,10 @@ __device__ __forceinline__ float4 finish_density(const Consts& c, float sum) {
 constexpr int kDT = 4;
 constexpr int kRgThreads = 1024;
 
-__global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
-                                                          int* __restrict__ gstart) {
+// the work of one block of kRgThreads threads (k_row_groups, and one phase of k_sort_small)
+__device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* cell_start, int* gstart) {
     __shared__ int s_warp[kRgThreads / 32];
     __shared__ int s_carry;
-    const int nx = gd->dims[0], nrows = gd->dims[1] * gd->dims[2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
@@ -144,6 +161,11 @@ __global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __res
         __syncthreads();
     }
     if (threadIdx.x == 0) gstart[nrows] = s_carry;
+}
+
+__global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                          int* __restrict__ gstart) {
+    row_groups_block(gd->dims[0], gd->dims[1] * gd->dims[2], cell_start, gstart);
 }
 
 // The row rho with gstart[rho] <= t < gstart[rho + 1] (t = density-group index).  One 32-ary search per WARP
@@ -237,17 +259,21 @@ __device__ __forceinline__ void density_row_single(const Consts& c, const float4
 #ifndef SPHB_DENSITY_MINBLOCKS
 #define SPHB_DENSITY_MINBLOCKS 8
 #endif
-template <bool kAux, bool kMask>
+// kLanes: 1, or 16 for small scenes: the 9 rows of a group go to 9 of 16 consecutive lanes (partial sums joined by
+// shuffles, each lane writes its own row's mask words), because with a few hundred groups the GPU is empty and what
+// counts is the length of one thread's chain: 972 particles (main.cpp's scene) 30 us -> see DESIGN.md.
+template <bool kAux, bool kMask, int kLanes = 1>
 __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                  const int* __restrict__ gstart,
                                                  const float4* __restrict__ posm, const float4* __restrict__ vel,
                                                  float4* __restrict__ aux, float4* __restrict__ vr,
                                                  unsigned int* __restrict__ mask, int n) {
     const GridDesc g = *gd;
-    const int t_raw = blockIdx.x * blockDim.x + threadIdx.x;
+    const int tg = blockIdx.x * blockDim.x + threadIdx.x;
+    const int t_raw = tg / kLanes, sub = tg % kLanes; // group, and which of its rows this lane takes (kLanes > 1)
     const int nrows_grid = g.dims[1] * g.dims[2];
     const int ngroups = __ldg(gstart + nrows_grid);
-    if ((t_raw & ~31) >= ngroups) return;          // whole warp beyond the last group
+    if ((tg & ~31) / kLanes >= ngroups) return;    // whole warp beyond the last group
     const bool live = t_raw < ngroups;
     const int t = live ? t_raw : ngroups - 1;       // spare lanes of the last warp shadow the last group (warp-wide votes below)
     const int lo_r = find_row(gstart, nrows_grid, t);
@@ -273,10 +299,11 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
         float2 acc01 = make_float2(0.0f, 0.0f), acc23 = make_float2(0.0f, 0.0f);
         // rows in canonical order r = (dz+S)*(2S+1) + (dy+S), counted without the divisions a runtime stencil would cost
         int dy_r = -S, dz_r = -S;
-        unsigned int* mrow = mask + i0; // word w of row r of target k: mrow[(2r+w)*n + k], advanced row by row
-        for (int r = 0; r < nrows; r++, mrow += 2 * (size_t)n) {
+        unsigned int* mrow = mask + i0 + 2 * (size_t)n * (kLanes > 1 ? sub : 0); // word w of row r of target k: mrow[(2r+w)*n + k]
+        for (int r = kLanes > 1 ? sub : 0; r < nrows; r += kLanes, mrow += 2 * (size_t)n * kLanes) {
+            if (kLanes > 1) { dz_r = r / (2 * S + 1) - S; dy_r = r % (2 * S + 1) - S; }
             const int z = cz[0] + dz_r, y = cy[0] + dy_r;
-            if (++dy_r > S) { dy_r = -S; ++dz_r; }
+            if (kLanes == 1 && ++dy_r > S) { dy_r = -S; ++dz_r; }
             int jbu = 0, jeu = 0, jbk[kDT] = {0, 0, 0, 0};
             const bool inside = !(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]);
             if (inside) {
@@ -375,6 +402,15 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
         }
         sum[0] += acc01.x; sum[1] += acc01.y; sum[2] += acc23.x; sum[3] += acc23.y;
     }
+    if (kLanes > 1) { // join the rows' partial sums; lane `sub == 0` of the group finishes
+        // groups leave as a whole, so a 16-lane segment is complete or gone: name exactly its lanes (the _sync re-converges them)
+        const unsigned int am = kLanes == 16 ? ((threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu) : 0xffffffffu;
+#pragma unroll
+        for (int k = 0; k < kDT; k++)
+#pragma unroll
+            for (int o = kLanes / 2; o > 0; o >>= 1) sum[k] += __shfl_xor_sync(am, sum[k], o);
+        if (sub != 0) return;
+    }
     if (kAux) {
 #pragma unroll
         for (int k = 0; k < kDT; k++) {
@@ -391,5 +427,85 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
         }
     }
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Small scenes: the whole grid build in ONE launch of one block.  At main.cpp's 972 particles the eight kernels
+// above are eight dependent launches of 3-5 us each for a few hundred nanoseconds of work; here their bodies run
+// back to back with block barriers in between -- same functions, same arithmetic, same stable order.
+__device__ __forceinline__ int scan_block_1024(int v, int* s_warp, int* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = s_warp[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        s_warp[lane] = w; // inclusive over warps
+    }
+    __syncthreads();
+    const int ex = (warp ? s_warp[warp - 1] : 0) + inc - v;
+    *total = s_warp[31];
+    __syncthreads(); // s_warp is reused
+    return ex;
+}
+
+template <bool kCarryAll>
+__global__ void __launch_bounds__(kRgThreads) k_sort_small(Consts c, BBoxAcc* acc, GridDesc* gd, int* cell_start, int* gstart,
+                                                          int* key, int* slot, int2* pairs, const int* __restrict__ oid_in,
+                                                          const float4* __restrict__ posm_in, const float4* __restrict__ vel_in,
+                                                          const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
+                                                          float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                                          float4* __restrict__ aux_out, float4* __restrict__ acc_out,
+                                                          int* __restrict__ oid_out, int n, int rearm_bbox, int trash) {
+    __shared__ GridDesc s_g;
+    __shared__ int s_scan[32];
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        derive_grid(c, acc, s_g);
+        *gd = s_g;
+    }
+    __syncthreads();
+    const GridDesc g = s_g;
+    if (rearm_bbox && tid < 3) { // after derive_grid has read the box: re-arm it for this step's force kernel
+        acc->lo[tid] = f2ord(INFINITY);
+        acc->hi[tid] = f2ord(-INFINITY);
+    }
+    for (int i = tid; i <= g.nbins; i += kRgThreads) cell_start[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += kRgThreads) { // K1
+        const float4 p = ldg4(posm_in + i);
+        int cx, cy, cz;
+        int k = cell_key(g, p.x, p.y, p.z, cx, cy, cz);
+        if (trash && p.w < 0.0f) k = g.ncell + (i & (kTrashBins - 1));
+        key[i] = k;
+        slot[i] = atomicAdd(cell_start + k, 1);
+    }
+    __syncthreads();
+    int carry = 0;
+    for (int base = 0; base <= g.nbins; base += kRgThreads) { // K2: exclusive scan in place
+        const int i = base + tid;
+        const int v = i <= g.nbins ? cell_start[i] : 0;
+        int tot;
+        const int ex = scan_block_1024(v, s_scan, &tot);
+        if (i <= g.nbins) cell_start[i] = carry + ex;
+        carry += tot;
+    }
+    __syncthreads();
+    row_groups_block(g.dims[0], g.dims[1] * g.dims[2], cell_start, gstart);
+    for (int i = tid; i < n; i += kRgThreads) pairs[cell_start[key[i]] + slot[i]] = make_int2(oid_in ? oid_in[i] : i, i); // K3
+    __syncthreads();
+    for (int p = tid; p < n; p += kRgThreads)
+        rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, g.ncell);
+}
+
 
 } // namespace sphb

@@ -209,6 +209,21 @@ int run_bbox(sphb_engine* e) {
     return SPHB_OK;
 }
 
+constexpr int kSmallSort = 8192; // particles up to which the grid build is one single-block launch
+
+// bookkeeping after either sort path: the new buffer is current, dead records are gone, derived data is stale
+int finish_sort(sphb_engine* e, int nxt) {
+    e->cur = nxt;
+    e->oid_identity = false; // the sort wrote the new buffer's ids
+    e->n -= e->n_dead; // the dead records now sit behind the live ones: [n, n + n_dead) of the new buffers, never read again
+    e->n_dead = 0;
+    e->grid_valid = true;
+    e->mask_valid = false;
+    e->vr_valid = false;
+    e->bbox_valid = false; // the key pass re-armed the accumulator
+    return SPHB_OK;
+}
+
 // K0..K3: grid description, keys, stable counting sort, reorder into the other ping-pong buffer.
 int run_sort(sphb_engine* e, bool carry_all) {
     const int n = (int)e->n;
@@ -220,6 +235,17 @@ int run_sort(sphb_engine* e, bool carry_all) {
     const int ntile_cap = cdiv(e->max_cells + 1 + kTrashBins, kScanTile);
     int setup_blocks = cdiv(e->max_cells + 1 + kTrashBins, 256 * 8);
     if (setup_blocks > 148 * 8) setup_blocks = 148 * 8;
+    if (n <= kSmallSort) { // small scene: the eight kernels below as phases of one single-block launch (same functions)
+        const int* oid_in = e->oid_identity ? (const int*)nullptr : e->oid[cur].p;
+        const int rearm = e->c.domain_fixed ? 0 : 1, trash = e->n_dead ? 1 : 0;
+#define SMALL_ARGS e->c, e->d_bbox, e->d_grid, e->cell_start.p, e->row_groups.p, e->key.p, e->slot.p, e->pairs.p, oid_in, e->posm[cur].p, \
+                   e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, rearm, trash
+        if (carry_all) LAUNCH(e, k_sort_small<true>, 1, kRgThreads, 0, SMALL_ARGS);
+        else LAUNCH(e, k_sort_small<false>, 1, kRgThreads, 0, SMALL_ARGS);
+#undef SMALL_ARGS
+        CK(cudaGetLastError());
+        return finish_sort(e, nxt);
+    }
     LAUNCH(e, k_grid_setup, setup_blocks, 256, 0, e->c, e->d_bbox, e->d_grid, e->cell_start.p);
     const int pb = cdiv(n, 256);
     LAUNCH(e, k_key_hist, pb, 256, 0, e->d_grid, e->posm[cur].p, n, e->key.p, e->slot.p, e->cell_start.p, e->d_bbox,
@@ -237,26 +263,28 @@ int run_sort(sphb_engine* e, bool carry_all) {
         LAUNCH(e, k_rank_gather<false>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
                e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid);
     CK(cudaGetLastError());
-    e->cur = nxt;
-    e->n -= e->n_dead; // the dead records now sit behind the live ones: [n, n + n_dead) of the new buffers, never read again
-    e->n_dead = 0;
-    e->grid_valid = true;
-    e->mask_valid = false;
-    e->vr_valid = false;
-    e->bbox_valid = false; // k_key_hist re-armed the accumulator
-    return SPHB_OK;
+    return finish_sort(e, nxt);
 }
 
 // K4.  with_aux = false only rebuilds the neighbour masks (update_forces on an uploaded rho/P).
+constexpr int kSmallScene = 32768; // particles up to which the latency-oriented kernel variants are used
+
 int run_density(sphb_engine* e, bool with_aux) {
     const int n = (int)e->n;
     if (n == 0) return SPHB_OK;
-    auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
     // groups <= n/kDT + (number of non-empty rows); threads beyond the device-side total exit at once
     long long rows_bound = e->max_cells < kMaxRows ? e->max_cells : kMaxRows;
     if (rows_bound > n) rows_bound = n;
-    LAUNCH(e, kfn, cdiv(cdiv(n, kDT) + rows_bound, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
-           e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, n);
+    const long long groups = cdiv(n, kDT) + rows_bound;
+    if (n <= kSmallScene && e->rows == 9) { // small scene: a group's rows side by side on 16 lanes (latency, not throughput)
+        auto kfs = with_aux ? k_density<true, true, 16> : k_density<false, true, 16>;
+        LAUNCH(e, kfs, cdiv(groups * 16, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+               e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, n);
+    } else {
+        auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
+        LAUNCH(e, kfn, cdiv(groups, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+               e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, n);
+    }
     CK(cudaGetLastError());
     e->mask_valid = true;
     e->vr_valid = with_aux;
