@@ -720,6 +720,9 @@ int sphb_step(sphb_engine* e, int nsteps) {
 #define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->vr.p, e->mask.p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
         auto kfn = bbox ? (acc ? force_kernel<true, true, true, true>(e->rows) : force_kernel<true, true, false, true>(e->rows))
                         : (acc ? force_kernel<true, false, true, true>(e->rows) : force_kernel<true, false, false, true>(e->rows));
+        if (n <= kSmallScene && e->rows == 9) // small scene: four neighbours in flight per thread (latency, not throughput)
+            kfn = bbox ? (acc ? k_force<true, true, true, 9, true, 4> : k_force<true, true, false, 9, true, 4>)
+                       : (acc ? k_force<true, false, true, 9, true, 4> : k_force<true, false, false, 9, true, 4>);
         LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS);
 #undef FORCE_ARGS
         CK(cudaGetLastError());

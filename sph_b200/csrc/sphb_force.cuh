@@ -89,7 +89,10 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
 // kDerive: gather (vx,vy,vz,rho) records written by k_density and derive P etc. from rho (two gathers per
 //          neighbour); otherwise gather vel and aux separately (three; needed when rho/P were uploaded and P
 //          need not equal k(rho - rho0)).
-template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive>
+// kIlp:   neighbours fetched per iteration.  1 for real workloads (more only cost registers there); 4 for small scenes,
+//         where a handful of warps per SM hide nothing and a thread's chain of L2-latency gathers IS the kernel time:
+//         four neighbours' records are requested before the first is used.  Same accumulation order, same bits.
+template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp = 1>
 __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
                                                const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
@@ -185,6 +188,37 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             pair_force(c, dx, dy, dz, d2, vi, ai, pj.w, vj, aj, ax, ay, az);
         };
         const int nstaged = kPairs ? min(nw, kCapW) : nw;
+        if (kIlp > 1 && kPairs && kDerive) {
+            for (;;) {
+                int jj[kIlp];
+                int got = 0;
+#pragma unroll
+                for (int u = 0; u < kIlp; u++) {
+                    if (m == 0 && k + 1 < nstaged) {
+                        const uint2 wb = s_wb[++k][tid];
+                        m = wb.x;
+                        jb = (int)wb.y;
+                    }
+                    jj[u] = m ? jb + __ffs((int)m) - 1 : -1;
+                    if (m) { m &= m - 1; got++; }
+                }
+                if (got == 0) break;
+                float4 pp[kIlp], vv[kIlp];
+#pragma unroll
+                for (int u = 0; u < kIlp; u++) {
+                    const int j = jj[u] >= 0 ? jj[u] : i;
+                    pp[u] = ldg4(posm + j);
+                    vv[u] = ldg4(vr + j);
+                }
+#pragma unroll
+                for (int u = 0; u < kIlp; u++) {
+                    if (jj[u] < 0) continue;
+                    const float dx = pi.x - pp[u].x, dy = pi.y - pp[u].y, dz = pi.z - pp[u].z;
+                    const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                    pair_force(c, dx, dy, dz, d2, vi, ai, pp[u].w, vv[u], aux_from_rho(c, vv[u].w), ax, ay, az);
+                }
+            }
+        } else
         for (;;) {
             if (m == 0) {
                 if (++k >= nstaged) break;
