@@ -85,3 +85,66 @@ def test_exchange_protocol_gloo(world, periodic):
         # what arrives from the left neighbour is what it sent to ITS right, and vice versa
         assert from_left == (10 * left + 2 if left is not None else -1.0)
         assert from_right == (10 * right + 1 if right is not None else -1.0)
+
+
+def _limit(capacity, last):
+    """SlabRank._limit without an engine: the size both ends of a link derive from the last message's record count."""
+    class _S:
+        adaptive = True
+    s = _S()
+    s.capacity = capacity
+    return multigpu.SlabRank._limit(s, last)
+
+
+def _worker_prefix(rank, world, port, q):
+    """Messages travel as prefixes whose length each end derives on its own: the sender from what it sent last step,
+    the receiver from what it received last step (the same number).  Bytes beyond the prefix must stay untouched."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        left, right = multigpu.neighbours(rank, world, periodic=True)
+        capacity = 65536
+        nbytes_full = 32 * (capacity + 1)
+        mk = lambda v: torch.full((nbytes_full,), v, dtype=torch.uint8)
+        out_l = out_r = in_l = in_r = capacity
+        ok = True
+        for step in range(4):
+            sent_l, sent_r = 100 + 7 * rank + step, 200 + 5 * rank + step         # records "packed" this step
+            send_left, send_right = mk(1 + rank), mk(101 + rank)
+            send_left[:8] = torch.frombuffer(np.array([sent_l, out_l], np.int32).tobytes(), dtype=torch.uint8)
+            send_right[:8] = torch.frombuffer(np.array([sent_r, out_r], np.int32).tobytes(), dtype=torch.uint8)
+            recv_left, recv_right = mk(255), mk(255)
+            nb = tuple(32 * (k + 1) for k in (out_l, out_r, in_l, in_r))
+            multigpu.exchange(dist, send_left, send_right, recv_left, recv_right, left, right, nb)
+            got_l = int(np.frombuffer(recv_left[:4].numpy().tobytes(), np.int32)[0])   # header: count from the left neighbour
+            got_r = int(np.frombuffer(recv_right[:4].numpy().tobytes(), np.int32)[0])
+            ok &= got_l == 200 + 5 * left + step and got_r == 100 + 7 * right + step
+            ok &= bool((recv_left[nb[2]:] == 255).all()) and bool((recv_right[nb[3]:] == 255).all())
+            ok &= int(recv_left[nb[2] - 1]) == 101 + left and int(recv_right[nb[3] - 1]) == 1 + right
+            out_l, out_r = _limit(capacity, sent_l), _limit(capacity, sent_r)
+            in_l, in_r = _limit(capacity, got_l), _limit(capacity, got_r)
+        q.put((rank, ok, out_l, out_r, in_l, in_r))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_prefix_exchange_sizes_agree_gloo():
+    world = 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_prefix, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(world):
+        rank, ok, out_l, out_r, in_l, in_r = q.get(timeout=120)
+        got[rank] = (ok, out_l, out_r, in_l, in_r)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, (ok, out_l, out_r, in_l, in_r) in got.items():
+        left, right = multigpu.neighbours(rank, world, periodic=True)
+        assert ok, f"rank {rank}: payload or untouched tail wrong"
+        assert out_r == got[right][3] and out_l == got[left][4]      # my next send size == what that neighbour will post
+        assert out_l < 65536 and out_r < 65536                       # and it really is a prefix
