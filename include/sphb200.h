@@ -251,12 +251,13 @@ typedef struct sphb_slab {
 /* Bytes of a message buffer that can carry `capacity` particles. */
 size_t sphb_mg_message_bytes(size_t capacity);
 
-/* Make room for up to n_max particles (owned + ghosts) before the first upload, so that the arrays need not
+/* Make room for up to n_max particles (owned + TWO generations of ghosts: the last step's stay in the arrays,
+ * marked dead, until the next step's sort drops them) before the first upload, so that the arrays need not
  * grow when neighbours send more than this rank started with. */
 int sphb_reserve(sphb_engine* e, size_t n_max);
 
-/* Classify the particles this rank owned by their current x: the ones it keeps (as owned or as ghosts) are
- * compacted into the engine's spare buffers, the ones a neighbour needs (its ghost zone, and migrants) into
+/* Classify the particles this rank owned by their current x: the ones it keeps (as owned or as ghosts) stay in
+ * their slots, the ones a neighbour needs (its ghost zone, and migrants) are copied into
  * msg_left / msg_right (either may be NULL when that neighbour does not exist).  Previous ghosts are dropped
  * (marked dead in place; a negative mass means "dead" to an engine that has used sphb_mg_pack).
  * Deterministic (order-preserving compaction of the messages).  Asynchronous on the engine's stream. */

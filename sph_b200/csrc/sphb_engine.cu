@@ -79,7 +79,7 @@ struct sphb_engine {
     SphereDev* d_spheres = nullptr; // kMaxSpheres records + one int (contact count) behind them
     int nspheres = 0;
     DevBuf<int2> contacts;  // particle-sphere contacts: (original id, slot), unsorted then sorted (2 x capacity)
-    DevBuf<int> mg_counts;  // multi-GPU pack: 3 per block, then totals[3] and recv_counts[4]
+    DevBuf<int> mg_counts;  // multi-GPU pack: 4 streams x tile counts, then totals[4], recv_counts[4] (+8 spare), one byte per warp
     int mg_blocks = 0;
     size_t mg_sent[2] = {0, 0}; // records the last pack put (wanted to put) into its left / right message, known after unpack
     bool mg_pending = false; // sphb_mg_pack ran, sphb_mg_unpack has not committed yet
