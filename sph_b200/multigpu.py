@@ -64,6 +64,32 @@ def quantile_bounds(x: np.ndarray, world: int, cell: float, lo: float, hi: float
     return [lo] + inner + [hi]
 
 
+def balanced_bounds(x: np.ndarray, world: int, cell: float, lo: float, hi: float, halo: float, iters: int = 40):
+    """Slab boundaries that equalise what a rank WORKS on -- its own particles plus the ghost layers of width `halo`
+    on both sides -- rather than what it owns: where particles are dense in x the quantile slabs get narrow and
+    their ghosts can be half a slab again (8-way strong scaling of the block drop).  Starts from the count
+    quantiles and moves every inner boundary towards the heavier neighbour; snapped to cell planes at the end."""
+    b = np.array(quantile_bounds(x, world, cell, lo, hi), np.float64)
+    if world < 2:
+        return list(b)
+    xs = np.sort(x.astype(np.float64))
+    count = lambda a, c: np.searchsorted(xs, c) - np.searchsorted(xs, a)
+    load = lambda bb: np.array([count(bb[r] - (halo if r else 0.0), bb[r + 1] + (halo if r < world - 1 else 0.0)) for r in range(world)], np.float64)
+    best, best_imb = b.copy(), np.inf
+    for _ in range(iters):
+        w = load(b)
+        imb = w.max() / w.mean()
+        if imb < best_imb:
+            best, best_imb = b.copy(), imb
+        for k in range(1, world):                       # boundary k separates ranks k-1 and k
+            width = min(b[k] - b[k - 1], b[k + 1] - b[k])
+            b[k] += 0.25 * width * (w[k] - w[k - 1]) / (w[k] + w[k - 1])   # rank k heavier: give rank k-1 more room
+        b[1:-1] = np.clip(b[1:-1], b[0] + 2 * halo, b[-1] - 2 * halo)
+        b[1:-1] = np.maximum.accumulate(b[1:-1])
+    inner = [lo + round((q - lo) / cell) * cell for q in best[1:-1]]
+    return [lo] + inner + [hi]
+
+
 def exchange(dist, send_left, send_right, recv_left, recv_right, left, right, nbytes=None):
     """Post the (at most) four point-to-point operations of one halo exchange and wait for them.
     Works on any backend (NCCL on device tensors, gloo on CPU tensors in the tests).  A rank that is its own
@@ -220,7 +246,7 @@ def bench_main(args, world, rank, local):
         if strong:
             # config 4 as written: ONE tank, N slabs whose boundaries sit at particle-count quantiles of x
             ps, walls = scenes.block_drop(scale=scale)
-            bounds = quantile_bounds(ps["pos"][:, 0], world, R, 0.0, section + 0.2)
+            bounds = balanced_bounds(ps["pos"][:, 0], world, R, 0.0, section + 0.2, halo)
             ps = ps[(ps["pos"][:, 0] >= (bounds[rank] if rank else -1e30)) & (ps["pos"][:, 0] < (bounds[rank + 1] if rank < world - 1 else 1e30))].copy()
         else:
             ps = scenes.block_drop_section(rank, world, scale=scale)
@@ -239,7 +265,7 @@ def bench_main(args, world, rank, local):
         face = (section + 0.2) * column * 1100.0                             # particles per unit x near a face (upper bound)
         capacity = int(face * halo * 2.0) + 4096
         eng.reserve(n_own + 4 * capacity)   # last step's ghosts stay (marked dead) until the next sort drops them
-        what = (f", ONE tank cut into {world} x-slabs at particle-count quantiles" if strong
+        what = (f", ONE tank cut into {world} x-slabs of equal owned-plus-ghost particle counts" if strong
                 else f", one tank section per GPU ({world} sections side by side)")
     sr = SlabRank(eng, slab, capacity, local)
 

@@ -44,6 +44,21 @@ def test_quantile_bounds_balance():
     assert all(abs((v / 0.2025) - round(v / 0.2025)) < 1e-9 for v in b[1:-1])       # snapped to cell planes
 
 
+def test_balanced_bounds_even_out_owned_plus_ghosts():
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(0, 24, 80000), rng.uniform(9, 15, 60000)])    # a dense column in the middle of a pool
+    halo, cell = 0.41, 0.2025
+    def imbalance(b):
+        w = [((x >= b[r] - (halo if r else 0)) & (x < b[r + 1] + (halo if r < 7 else 0))).sum() for r in range(8)]
+        return max(w) / np.mean(w)
+    q = multigpu.quantile_bounds(x, 8, cell, 0.0, 24.0)
+    b = multigpu.balanced_bounds(x, 8, cell, 0.0, 24.0, halo)
+    assert b[0] == 0.0 and b[-1] == 24.0 and all(b[i] < b[i + 1] for i in range(8))
+    assert all(abs((v / cell) - round(v / cell)) < 1e-9 for v in b[1:-1])
+    assert imbalance(b) < imbalance(q) and imbalance(b) < 1.12
+    assert multigpu.balanced_bounds(x, 1, cell, 0.0, 24.0, halo) == [0.0, 24.0]
+
+
 def _worker(rank, world, port, periodic, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
