@@ -106,6 +106,21 @@ class Oracle:
         else:
             self.lib.orc_viscosity_forces_allpairs(self.p, _vp(ps), C.c_size_t(len(ps)))
 
+    # --- FP64 referee (same formulas, double arithmetic, float inputs): how far the reference's own rounding is from exact
+    def density_f64(self, ps, threads=0) -> np.ndarray:
+        """Unclamped density sum per particle in double."""
+        out = np.zeros(len(ps), np.float64)
+        self.lib.orc_density_f64_cells(self.p, _vp(ps), C.c_size_t(len(ps)), _vp(out), C.c_int(threads))
+        return out
+
+    def forces_f64(self, ps, threads=0):
+        """(accel[n,3], scale[n]) in double from the float state in ps (its density / pressure fields as given);
+        scale = 1 + sum_j |temp_ij| |gradW_ij| (SURVEY.md H2 normaliser)."""
+        acc = np.zeros((len(ps), 3), np.float64)
+        scale = np.zeros(len(ps), np.float64)
+        self.lib.orc_forces_f64_cells(self.p, _vp(ps), C.c_size_t(len(ps)), _vp(acc), _vp(scale), C.c_int(threads))
+        return acc, scale
+
     def update_posvel(self, ps, spheres=None):
         ns = 0 if spheres is None else len(spheres)
         self.lib.orc_update_posvel(self.p, _vp(ps), C.c_size_t(len(ps)), _vp(spheres) if ns else None, C.c_size_t(ns))

@@ -538,6 +538,90 @@ void orc_viscosity_forces_cells(const orc_params* p, orc_particle* ps, size_t n,
     cellctx_free(&c);
 }
 
+/* ---- FP64 referee: the same formulas evaluated in double on the same float inputs ------ */
+/* Not a restatement of reference code: it answers "how far is the reference's own float arithmetic from the
+ * exact value of its formulas", so that a reader can see how much of a GPU-vs-reference difference is the
+ * reference's rounding.  rho_raw[n]: the unclamped density sum.  Neighbours in any order (double sums). */
+void orc_density_f64_cells(const orc_params* p, const orc_particle* ps, size_t n, double* rho_raw, int threads) {
+    if (n == 0) return;
+    cellctx c;
+    cellctx_init(&c, p, ps, n);
+    const double h = (double)p->h, kw = 315.0 / (64.0 * (double)ORC_PI_F * pow(h, 9));
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel num_threads(threads)
+#endif
+    {
+        int cap = 512;
+        int* buf = (int*)malloc(sizeof(int) * cap);
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 256)
+#endif
+        for (long long i = 0; i < (long long)n; i++) {
+            int cnt = gather_sorted(&c, p, ps, (size_t)i, &buf, &cap);
+            double sum = 0.0;
+            for (int k = 0; k < cnt; k++) {
+                const orc_particle* b = &ps[buf[k]];
+                double dx = (double)ps[i].pos[0] - b->pos[0], dy = (double)ps[i].pos[1] - b->pos[1], dz = (double)ps[i].pos[2] - b->pos[2];
+                double q = sqrt(dx * dx + dy * dy + dz * dz) / h;
+                if (q <= h) {
+                    double t = h * h - q * q;
+                    sum += (double)b->mass * kw * t * t * t;
+                }
+            }
+            rho_raw[i] = sum;
+        }
+        free(buf);
+    }
+    cellctx_free(&c);
+}
+
+/* acc[3n]: gravity + pair sum (SphUtils.cpp:219-230) in double from the float pos, vel, mass, density, pressure in ps;
+ * scale[n] = 1 + sum_j |temp_ij| |gradW_ij|: the magnitude against which a cancelling sum is accurate. */
+void orc_forces_f64_cells(const orc_params* p, const orc_particle* ps, size_t n, double* acc_out, double* scale, int threads) {
+    if (n == 0) return;
+    cellctx c;
+    cellctx_init(&c, p, ps, n);
+    const double h = (double)p->h, kg = -45.0 / ((double)ORC_PI_F * pow(h, 6));
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel num_threads(threads)
+#endif
+    {
+        int cap = 512;
+        int* buf = (int*)malloc(sizeof(int) * cap);
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 256)
+#endif
+        for (long long i = 0; i < (long long)n; i++) {
+            int cnt = gather_sorted(&c, p, ps, (size_t)i, &buf, &cap);
+            const orc_particle* a = &ps[i];
+            double acc[3] = {0.0, -1.0, 0.0}, sc = 1.0;
+            for (int k = 0; k < cnt; k++) {
+                const orc_particle* b = &ps[buf[k]];
+                double dx[3], dv[3];
+                for (int d = 0; d < 3; d++) { dx[d] = (double)a->pos[d] - b->pos[d]; dv[d] = (double)a->vel[d] - b->vel[d]; }
+                double r2 = dx[0] * dx[0] + dx[1] * dx[1] + dx[2] * dx[2], r = sqrt(r2), q = r / h;
+                if (!(q < h)) continue;
+                double vdotr = dv[0] * dx[0] + dv[1] * dx[1] + dv[2] * dx[2], pi = 0.0;
+                if (vdotr < 0) {
+                    double cb = (sqrt(fabs((double)a->pressure / a->density)) + sqrt(fabs((double)b->pressure / b->density))) / 2.0;
+                    double mu = h * vdotr / (r2 + 0.01 * h * h);
+                    pi = 2.0 * (-0.1 * cb * mu + 0.2 * mu * mu) / ((double)a->density + b->density);
+                }
+                double temp = -(double)b->mass * (pi + ((double)a->pressure + b->pressure) / (2.0 * b->density * a->density));
+                double g = kg * (h - q) * (h - q);
+                for (int d = 0; d < 3; d++) acc[d] += temp * g * dx[d] / r;
+                sc += fabs(temp * g);
+            }
+            acc_out[3 * i] = acc[0]; acc_out[3 * i + 1] = acc[1]; acc_out[3 * i + 2] = acc[2];
+            if (scale) scale[i] = sc;
+        }
+        free(buf);
+    }
+    cellctx_free(&c);
+}
+
 void orc_step_cells(const orc_params* p, orc_particle* ps, size_t n, const orc_wall* w, size_t nw, int nsteps, int threads) {
     for (int k = 0; k < nsteps; k++) {
         orc_update_density_cells(p, ps, n, threads);

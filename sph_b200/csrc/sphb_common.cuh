@@ -71,8 +71,8 @@ __device__ __forceinline__ float ord2f(unsigned int u) {
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
-// MUFU approximations without the denormal fix-up code the C library versions carry (the pair body runs
-// ~40 times per particle per step; magnitudes here are nowhere near 1e-38).  <= 2 ulp each.
+// MUFU approximations without the denormal fix-up code the C library versions carry (magnitudes here are nowhere
+// near 1e-38).  <= 2 ulp each; seeds of the pm_* functions below.
 __device__ __forceinline__ float fast_rsqrt(float x) {
     float r;
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -89,12 +89,49 @@ __device__ __forceinline__ float fast_sqrt(float x) {
     return r;
 }
 
+// The special functions of the pair body (SphUtils.cpp:223-228 divides and takes square roots in IEEE float).
+// SPHB_PAIR_MATH selects how close to that they get:
+//   0  raw MUFU approximations (<= 2 ulp each; round 1)
+//   1  MUFU seed + one Newton step for 1/x and 1/sqrt(x) (<= 1 ulp), correctly rounded sqrt     [default]
+//   2  correctly rounded everywhere (__frcp_rn / __frsqrt_rn / __fsqrt_rn)
+// Measured on B200 (Numerics): time and per-particle error of all three.
+#ifndef SPHB_PAIR_MATH
+#define SPHB_PAIR_MATH 1
+#endif
+__device__ __forceinline__ float pm_rsqrt(float x) {
+#if SPHB_PAIR_MATH == 0
+    return fast_rsqrt(x);
+#elif SPHB_PAIR_MATH == 1
+    const float r = fast_rsqrt(x);
+    return fmaf(r, fmaf(-0.5f * x * r, r, 0.5f), r); // r + r (1/2 - x r^2 / 2); x = 0 stays non-finite -> NaN downstream, like normalize(0)
+#else
+    return __frsqrt_rn(x);
+#endif
+}
+__device__ __forceinline__ float pm_rcp(float x) {
+#if SPHB_PAIR_MATH == 0
+    return fast_rcp(x);
+#elif SPHB_PAIR_MATH == 1
+    const float r = fast_rcp(x);
+    return fmaf(r, fmaf(-x, r, 1.0f), r);
+#else
+    return __frcp_rn(x);
+#endif
+}
+__device__ __forceinline__ float pm_sqrt(float x) {
+#if SPHB_PAIR_MATH == 0
+    return fast_sqrt(x);
+#else
+    return __fsqrt_rn(x);
+#endif
+}
+
 // aux record (rho, P, sqrt|P/rho|, 1/rho).  The last two are helpers of the pair body (SphUtils.cpp:223,228),
 // never returned to the host; they are computed by this ONE function wherever they are needed (density
 // kernel, upload, per-neighbour re-derivation) so that every path sees the same bits.
 __device__ __forceinline__ float4 make_aux(float rho, float P) {
-    const float inv = fast_rcp(rho);
-    return make_float4(rho, P, fast_sqrt(fabsf(P * inv)), inv);
+    const float inv = pm_rcp(rho);
+    return make_float4(rho, P, pm_sqrt(fabsf(P * inv)), inv);
 }
 
 // Cell coordinate along one axis.  Same expression as SphUtils.cpp:38-40, floor((p - min) / cell), in

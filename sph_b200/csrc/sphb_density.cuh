@@ -256,6 +256,11 @@ __device__ __forceinline__ void density_row_single(const Consts& c, const float4
 // 8 resident blocks of 128 threads per SM (64 registers): measured best on B200 -- the loop is latency-bound,
 // so occupancy beats the few spilled words (1: 2.38 ms, 6: 2.41, 7: 2.21, 8: 2.16 ms per 16.7 M particles;
 // a register-staged software prefetch of the candidates bought nothing on top).
+// SPHB_DENSITY_WFORM 1: the packed loop accumulates m min(d2 - R^2, 0)^3 and the factor -1/h^6 is applied once per
+// target after the loop (one packed multiply less per candidate and target pair); 0: m max(h^2 - d2/h^2, 0)^3 per candidate.
+#ifndef SPHB_DENSITY_WFORM
+#define SPHB_DENSITY_WFORM 1
+#endif
 #ifndef SPHB_DENSITY_MINBLOCKS
 #define SPHB_DENSITY_MINBLOCKS 8
 #endif
@@ -342,10 +347,15 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
                             m[1] = __funnelshift_l(__float_as_uint(u.y), m[1], 1);
                         }
                         if (kAux) {
+#if SPHB_DENSITY_WFORM
+                            const float2 v = make_float2(fminf(u.x, 0.0f), fminf(u.y, 0.0f)); // min(d2 - R^2, 0) = -h^2 max(t, 0)
+                            acc01 = __ffma2_rn(__fmul2_rn(v, v), __fmul2_rn(mm, v), acc01);
+#else
                             float2 t = __fmul2_rn(u, nih2);
                             t.x = fmaxf(t.x, 0.0f);
                             t.y = fmaxf(t.y, 0.0f);
                             acc01 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc01);
+#endif
                         }
                     }
                     {
@@ -357,10 +367,15 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
                             m[3] = __funnelshift_l(__float_as_uint(u.y), m[3], 1);
                         }
                         if (kAux) {
+#if SPHB_DENSITY_WFORM
+                            const float2 v = make_float2(fminf(u.x, 0.0f), fminf(u.y, 0.0f)); // min(d2 - R^2, 0) = -h^2 max(t, 0)
+                            acc23 = __ffma2_rn(__fmul2_rn(v, v), __fmul2_rn(mm, v), acc23);
+#else
                             float2 t = __fmul2_rn(u, nih2);
                             t.x = fmaxf(t.x, 0.0f);
                             t.y = fmaxf(t.y, 0.0f);
                             acc23 = __ffma2_rn(mm, __fmul2_rn(__fmul2_rn(t, t), t), acc23);
+#endif
                         }
                     }
                 };
@@ -400,7 +415,13 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
                 }
             }
         }
+#if SPHB_DENSITY_WFORM
+        // the packed loop summed m (d2 - R^2)^3 over the neighbours: W ~ (h^2 - d2/h^2)^3 = -(d2 - R^2)^3 / h^6
+        const float k3 = -(c.inv_h2 * c.inv_h2 * c.inv_h2);
+        sum[0] = fmaf(k3, acc01.x, sum[0]); sum[1] = fmaf(k3, acc01.y, sum[1]); sum[2] = fmaf(k3, acc23.x, sum[2]); sum[3] = fmaf(k3, acc23.y, sum[3]);
+#else
         sum[0] += acc01.x; sum[1] += acc01.y; sum[2] += acc23.x; sum[3] += acc23.y;
+#endif
     }
     if (kLanes > 1) { // join the rows' partial sums; lane `sub == 0` of the group finishes
         // groups leave as a whole, so a 16-lane segment is complete or gone: name exactly its lanes (the _sync re-converges them)

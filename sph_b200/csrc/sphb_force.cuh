@@ -15,14 +15,14 @@ namespace sphb {
 __device__ __forceinline__ float pair_weight(const Consts& c, float dx, float dy, float dz, float d2, const float4& vi, const float4& ai,
                                              float mj, const float4& vj, const float4& aj) {
     const float vdotr = fmaf(vi.x - vj.x, dx, fmaf(vi.y - vj.y, dy, (vi.z - vj.z) * dz)); // :220
-    const float rinv = fast_rsqrt(d2);
+    const float rinv = pm_rsqrt(d2);
     const float r = d2 * rinv;
     const float s = fmaf(-r, c.inv_h, c.h); // h - q, q = r/h              (:70-74)
     float visc = 0.0f;
     if (vdotr < 0.0f) {                                                                  // :222-227
         const float cbar = 0.5f * (ai.z + aj.z);
-        const float mu = c.h * vdotr * fast_rcp(d2 + c.eta_h2);
-        visc = 2.0f * mu * fmaf(c.beta, mu, -c.alpha * cbar) * fast_rcp(ai.x + aj.x);
+        const float mu = c.h * vdotr * pm_rcp(d2 + c.eta_h2);
+        visc = 2.0f * mu * fmaf(c.beta, mu, -c.alpha * cbar) * pm_rcp(ai.x + aj.x);
     }
     // :228  -(m_j) * (pi + (P_i + P_j) / (2 rho_j rho_i)); ai.w, aj.w = 1/rho
     const float t = -mj * fmaf(0.5f * (ai.y + aj.y), ai.w * aj.w, visc);
@@ -38,7 +38,7 @@ __device__ __forceinline__ void pair_force(const Consts& c, float dx, float dy, 
 }
 
 // The neighbour's (P, sqrt|P/rho|, 1/rho) from its rho alone, as finish_density computes them (P with the
-// same rounding; the other two through MUFU approximations, <= 2 ulp).
+// same rounding; the other two through make_aux, i.e. the same bits the density kernel stored).
 __device__ __forceinline__ float4 aux_from_rho(const Consts& c, float rho) {
     return make_aux(rho, __fmul_rn(c.eos_k, __fsub_rn(rho, c.rho0)));
 }

@@ -189,8 +189,11 @@ def test_full_size_parity_against_the_oracle(oracle, name):
         e.update_forces()
         e.download(fed, sph_b200.F_ACCEL)
     err = np.linalg.norm(fed["accel"].astype(np.float64) - want["accel"], axis=1)
-    # scale: 1 + |a| is a LOWER bound of the 1 + sum|terms| used at small sizes (the exact sum needs a pair list of
-    # ~3e8 entries here), so this is the stricter normalisation
-    scale = 1.0 + np.linalg.norm(want["accel"].astype(np.float64), axis=1)
-    print(f"{name}: n={n} compressed fraction {compressed:.3f} density err {rel.max():.2e} accel err {np.max(err / scale):.2e}")
-    assert np.max(err / scale) <= 5e-5
+    # SURVEY.md H2 normaliser, 1 + sum_j |temp_ij| |gradW_ij| per particle, from the oracle's FP64 pass over the same cell
+    # list (a pair list of ~3e8 entries would not fit the scipy route the small sizes use); north_star's 1e-5.
+    a64, scale = oracle.forces_f64(want)
+    del a64
+    plain = err / np.maximum(np.linalg.norm(want["accel"].astype(np.float64), axis=1), 1e-30)
+    print(f"{name}: n={n} compressed fraction {compressed:.3f} density err {rel.max():.2e} accel err normalised {np.max(err / scale):.2e}, "
+          f"plain max {plain.max():.2e} p99.9 {np.quantile(plain, 0.999):.2e} above 1e-5: {(plain > 1e-5).sum()}")
+    assert np.max(err / scale) <= 1e-5

@@ -58,3 +58,18 @@ def test_dam64k_cell_list_equals_reference_all_pairs(oracle, golden):
     assert sha(ps["pressure"]) == str(g["sha_pressure"])
     assert sha(ps["accel"]) == str(g["sha_accel"])
     assert ps["density"][::16].tobytes() == g["sub_density"].tobytes()
+
+
+def test_fp64_referee_brackets_the_reference_rounding(oracle, golden):
+    """The FP64 evaluation of the reference's formulas (oracle.density_f64 / forces_f64, the referee of SURVEY.md H2)
+    agrees with the reference's own float results to the level float rounding explains: density <= 1e-6 relative,
+    acceleration <= 1e-6 of 1 + sum|terms| (plain relative error is larger where terms cancel, <= 5e-5 here)."""
+    g = golden("block4096.npz")
+    ps = g["density"].copy()                       # state after the reference's update_density
+    rho64 = np.maximum(oracle.density_f64(g["initial"]), 10.0)
+    assert np.max(np.abs(ps["density"] - rho64) / rho64) <= 1e-6
+    a64, scale = oracle.forces_f64(ps)
+    d = np.linalg.norm(g["forces"]["accel"].astype(np.float64) - a64, axis=1)
+    assert np.all(scale >= 1.0)
+    assert np.max(d / scale) <= 1e-6
+    assert np.max(d / np.linalg.norm(a64, axis=1)) <= 5e-5
