@@ -72,8 +72,10 @@ typedef struct sphb_params {
     int32_t domain_mode;   /* SPHB_DOMAIN_* */
     float domain_lo[3];    /* used when domain_mode == SPHB_DOMAIN_FIXED */
     float domain_hi[3];
-    int32_t periodic[3];   /* per axis: 1 => minimum-image wrap over [domain_lo, domain_hi) (needs FIXED). Extension:
-                              the reference has only planes */
+    int32_t periodic_reserved[3]; /* must be 0.  Periodic boxes (an extension: the reference has only planes) are set up through
+                              sphb_slab -- shift_left/right for x, periodic_y/z for the other two -- and sphb_mg_pack, where they
+                              become ghost images; a single engine is then its own x-neighbour.  The kernels carry no
+                              minimum-image code */
     int64_t max_cells;     /* capacity of the cell table; 0 => chosen from the particle count at upload */
     int32_t write_accel;   /* 1 => sphb_step also stores per-particle acceleration (parity / viewers); 0 => skipped */
     int32_t cell_x_div;    /* the grid cell is cell_size / cell_x_div long in x (cell_size in y and z): the cells of a
@@ -189,10 +191,26 @@ int sphb_get_timing(sphb_engine* e, float ms[4], int* steps);
 /* Kernel launches issued by this engine since creation (for bench.py's gpu_launches). */
 uint64_t sphb_launch_count(const sphb_engine* e);
 
+/* Counters since the engine was created (nothing like them in the reference, which has no diagnostics at all).
+ * arrival_order_cells: how many times a grid cell held more than 4,096 particles at sort time and therefore kept the
+ * (not reproducible) arrival order instead of the stable one -- only pathological states do this: everything clamped
+ * into one boundary cell, or a state gone NaN.  0 means every sort so far produced the stable permutation.  Synchronises. */
+typedef struct sphb_stats {
+    uint64_t arrival_order_cells;
+    uint64_t steps;      /* sphb_step steps run */
+    uint64_t launches;   /* = sphb_launch_count */
+    uint64_t particles;  /* = sphb_count */
+    uint64_t capacity;   /* particle records the arrays can hold without growing */
+    uint64_t reserved[3];
+} sphb_stats;
+int sphb_get_stats(sphb_engine* e, sphb_stats* out);
+
 /* --- device-resident access for the headless bench and the multi-GPU driver ----------------------- */
 
 /* Upload from DEVICE SoA arrays (float4 posm = x,y,z,mass; float4 vel = vx,vy,vz,0), n particles,
- * device-to-device on the engine's stream.  ids (may be NULL) = caller's 32-bit particle ids. */
+ * device-to-device on the engine's stream.  ids (may be NULL = 0..n-1) names each particle's place in the "original
+ * order" that downloads return: it must be a permutation of 0..n-1.  Anything else is refused with SPHB_ERR_INVALID
+ * (checked on the device; that check synchronises) and leaves the engine without a state. */
 int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, const int32_t* ids, size_t n);
 /* Current device pointers (sorted order, valid until the next call that steps or uploads):
  * posm float4, vel float4, aux float4 (density, pressure, sqrt|P/rho|, 1/rho), accel float4, ids int32. */

@@ -232,6 +232,12 @@ class Reference:
         except Exception:
             pass
 
+    def default_mvp(self) -> np.ndarray:
+        """MVP of main.cpp:48-60 computed by the reference's vendored GLM (column-major, 16 floats)."""
+        m = np.zeros(16, np.float32)
+        self.lib.ref_default_mvp(_vp(m))
+        return m
+
     def kernel_function(self, i, j) -> float:
         return float(self.lib.ref_kernel_function(self.h, _f3(i), _f3(j)))
 

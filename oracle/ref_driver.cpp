@@ -15,6 +15,7 @@
 #include <vector>
 
 #include <glm/glm.hpp>            // guarded: pulled in before the keyword trick below
+#include <glm/gtc/matrix_transform.hpp>  // glm::perspective / glm::lookAt, header-only (deps/include/glm/gtc/matrix_transform.inl)
 
 #define private public            // read bbox / cells for the update_cells pin (SphUtils.hpp:46-57)
 #include "SphUtils.hpp"
@@ -163,4 +164,15 @@ int ref_update_cells(void* s, void* particles, size_t n, float* out_bbox, int* o
     return (int)u->cells.size();
 }
 
+
+// The viewer's camera: the GLM calls of SPH/main.cpp:48-60 (a file-scope global there; main.cpp itself needs GL
+// headers and cannot be compiled here) evaluated by the reference's own vendored GLM 0.9.6.1 with main.cpp's
+// arguments.  Column-major, 16 floats, as glUniformMatrix4fv(..., GL_FALSE, &MVP[0][0]) would send it.
+void ref_default_mvp(float out[16]) {
+    glm::mat4 Projection = glm::perspective(45.0f, 4.0f / 3.0f, 0.1f, 100.0f);                                       // main.cpp:48
+    glm::mat4 View = glm::lookAt(glm::vec3(0.0f, -0.8f, 1.5f), glm::vec3(0.0f, -0.8f, 0.0f), glm::vec3(0.0f, 1.0f, 0.0f));  // :50-54
+    glm::mat4 Model = glm::mat4(1.0f);                                                                                // :57
+    glm::mat4 MVP = Projection * View * Model;                                                                        // :60
+    std::memcpy(out, &MVP[0][0], 16 * sizeof(float));
+}
 }  // extern "C"

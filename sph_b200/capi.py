@@ -47,6 +47,13 @@ class Slab(C.Structure):
                 ("ylo", C.c_float), ("ylen", C.c_float), ("zlo", C.c_float), ("zlen", C.c_float)]
 
 
+class Stats(C.Structure):
+    """struct sphb_stats (include/sphb200.h)."""
+
+    _fields_ = [("arrival_order_cells", C.c_uint64), ("steps", C.c_uint64), ("launches", C.c_uint64), ("particles", C.c_uint64),
+                ("capacity", C.c_uint64), ("reserved", C.c_uint64 * 3)]
+
+
 class Params(C.Structure):
     """struct sphb_params (include/sphb200.h)."""
 
@@ -57,7 +64,7 @@ class Params(C.Structure):
         ("restitution", C.c_float), ("cell_size", C.c_float),
         ("wall_test_off", C.c_double), ("wall_test_lim", C.c_double),
         ("domain_mode", C.c_int32), ("domain_lo", C.c_float * 3), ("domain_hi", C.c_float * 3),
-        ("periodic", C.c_int32 * 3), ("max_cells", C.c_int64), ("write_accel", C.c_int32),
+        ("periodic_reserved", C.c_int32 * 3), ("max_cells", C.c_int64), ("write_accel", C.c_int32),
         ("cell_x_div", C.c_int32), ("laplacian_viscosity", C.c_int32), ("lap_visc_coef", C.c_float), ("reserved", C.c_int32 * 4),
     ]
 
@@ -69,7 +76,7 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent",
+    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats",
 ]
 
 _lib = None
@@ -136,6 +143,7 @@ def load_library() -> C.CDLL:
     L.sphb_mg_unpack.argtypes = [vp, C.POINTER(Slab), vp, vp, C.POINTER(sz * 4)]
     L.sphb_mg_sent.argtypes = [vp, C.POINTER(sz * 2)]
     L.sphb_mg_pack_limits.argtypes = [vp, C.POINTER(Slab), vp, sz, vp, sz]
+    L.sphb_get_stats.argtypes = [vp, C.POINTER(Stats)]
     _lib = L
     return L
 
@@ -363,6 +371,11 @@ class Engine:
         k = C.c_int(0)
         self._check(self.lib.sphb_get_timing(self.h, _ptr(t), C.byref(k)))
         return t, k.value
+
+    def stats(self) -> dict:
+        st = Stats()
+        self._check(self.lib.sphb_get_stats(self.h, C.byref(st)))
+        return {k: int(getattr(st, k)) for k, _ in Stats._fields_ if k != "reserved"}
 
     def launch_count(self) -> int:
         return int(self.lib.sphb_launch_count(self.h))

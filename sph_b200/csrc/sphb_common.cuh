@@ -18,7 +18,7 @@ constexpr int kTrashBins = 1024;
 
 struct GridDesc {
     float origin[3];
-    float cell[3]; // per axis (equal unless an axis is periodic and the cell was stretched to tile it)
+    float cell[3]; // per axis: cell / cell_x_div in x, cell in y and z
     int dims[3];
     int ncell;     // dims[0]*dims[1]*dims[2]
     int nbins;     // ncell + kTrashBins: counters / scan length (the extra bins collect records marked dead, see k_key_hist)
@@ -50,7 +50,6 @@ struct Consts {
     float wu[kMaxWalls][3];     // normalize(normal), computed on the host with IEEE float ops
     int domain_fixed;
     float dom_lo[3], dom_hi[3];
-    int periodic[3];
     long long max_cells;
     float lap_coef; // coefficient of the optional Laplacian viscosity (SphUtils.cpp:277), 0 when off
     float cell;   // cell edge in y and z

@@ -29,7 +29,7 @@ __device__ __forceinline__ void rank_gather_one(int p, const int2* pairs, const 
                                                 const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                 float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                 float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                int* __restrict__ oid_out, int ncell);
+                                                int* __restrict__ oid_out, int ncell, unsigned int* __restrict__ stats);
 
 template <bool kCarryAll>
 __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pairs, const int* __restrict__ key, const int* __restrict__ cell_start,
@@ -37,10 +37,11 @@ __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pa
                                                      const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                      float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                      float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                     int* __restrict__ oid_out, int n, const GridDesc* __restrict__ gd) {
+                                                     int* __restrict__ oid_out, int n, const GridDesc* __restrict__ gd,
+                                                     unsigned int* __restrict__ stats) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, gd->ncell);
+    rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, gd->ncell, stats);
 }
 
 template <bool kCarryAll>
@@ -49,7 +50,7 @@ __device__ __forceinline__ void rank_gather_one(int p, const int2* pairs, const 
                                                 const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                 float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                 float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                int* __restrict__ oid_out, int ncell) {
+                                                int* __restrict__ oid_out, int ncell, unsigned int* __restrict__ stats) {
     const int2 me = pairs[p];
     const int k = key[me.y];
     if (k >= ncell) return; // a trash bin: records the slab exchange marked dead end here and are not carried over
@@ -59,6 +60,7 @@ __device__ __forceinline__ void rank_gather_one(int p, const int2* pairs, const 
         for (int q = b; q < e; q++) rank += (pairs[q].x < me.x);
     } else {
         rank = p - b; // arrival order
+        if (p == b) atomicAdd(stats, 1u); // one count per such cell and sort (sphb_get_stats: arrival_order_cells)
     }
     const int dst = b + rank;
     posm_out[dst] = ldg4(posm_in + me.y);
@@ -486,7 +488,8 @@ __global__ void __launch_bounds__(kRgThreads) k_sort_small(Consts c, BBoxAcc* ac
                                                           const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                           float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                           float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                          int* __restrict__ oid_out, int n, int rearm_bbox, int trash) {
+                                                          int* __restrict__ oid_out, int n, int rearm_bbox, int trash,
+                                                          unsigned int* __restrict__ stats) {
     __shared__ GridDesc s_g;
     __shared__ int s_scan[32];
     const int tid = threadIdx.x;
@@ -525,7 +528,7 @@ __global__ void __launch_bounds__(kRgThreads) k_sort_small(Consts c, BBoxAcc* ac
     for (int i = tid; i < n; i += kRgThreads) pairs[cell_start[key[i]] + slot[i]] = make_int2(oid_in ? oid_in[i] : i, i); // K3
     __syncthreads();
     for (int p = tid; p < n; p += kRgThreads)
-        rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, g.ncell);
+        rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, g.ncell, stats);
 }
 
 

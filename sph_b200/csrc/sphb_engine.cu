@@ -86,6 +86,8 @@ struct sphb_engine {
     size_t reserved = 0;
     GridDesc* d_grid = nullptr;
     BBoxAcc* d_bbox = nullptr;
+    unsigned int* d_stats = nullptr; // [0] cells whose stable rank fell back to arrival order (cumulative), [1..3] spare
+    uint64_t steps_done = 0;
     long long max_cells = 0;
 
     bool have_state = false;
@@ -155,7 +157,6 @@ void build_consts(sphb_engine* e) {
     for (int a = 0; a < 3; a++) {
         c.dom_lo[a] = p.domain_lo[a];
         c.dom_hi[a] = p.domain_hi[a];
-        c.periodic[a] = p.periodic[a];
     }
     c.lap_coef = p.laplacian_viscosity ? p.lap_visc_coef : 0.0f;
     c.cell = p.cell_size > 0.0f ? p.cell_size : c.h2;
@@ -239,7 +240,7 @@ int run_sort(sphb_engine* e, bool carry_all) {
         const int* oid_in = e->oid_identity ? (const int*)nullptr : e->oid[cur].p;
         const int rearm = e->c.domain_fixed ? 0 : 1, trash = e->n_dead ? 1 : 0;
 #define SMALL_ARGS e->c, e->d_bbox, e->d_grid, e->cell_start.p, e->row_groups.p, e->key.p, e->slot.p, e->pairs.p, oid_in, e->posm[cur].p, \
-                   e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, rearm, trash
+                   e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, rearm, trash, e->d_stats
         if (carry_all) LAUNCH(e, k_sort_small<true>, 1, kRgThreads, 0, SMALL_ARGS);
         else LAUNCH(e, k_sort_small<false>, 1, kRgThreads, 0, SMALL_ARGS);
 #undef SMALL_ARGS
@@ -258,10 +259,10 @@ int run_sort(sphb_engine* e, bool carry_all) {
     e->oid_identity = false; // k_rank_gather writes the new buffer's ids
     if (carry_all)
         LAUNCH(e, k_rank_gather<true>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid);
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid, e->d_stats);
     else
         LAUNCH(e, k_rank_gather<false>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid);
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid, e->d_stats);
     CK(cudaGetLastError());
     return finish_sort(e, nxt);
 }
@@ -357,7 +358,8 @@ int sphb_create(const sphb_params* p, int device, sphb_engine** out) {
     const float R = p->h * p->h;
     if (p->cell_size != 0.0f && !(p->cell_size >= 0.5f * R)) return fail(SPHB_ERR_INVALID, "cell_size must be 0 or >= h*h/2");
     if (p->domain_mode != SPHB_DOMAIN_BBOX && p->domain_mode != SPHB_DOMAIN_FIXED) return fail(SPHB_ERR_INVALID, "bad domain_mode");
-    if (p->periodic[0] || p->periodic[1] || p->periodic[2]) return fail(SPHB_ERR_INVALID, "periodic axes are not implemented yet");
+    if (p->periodic_reserved[0] || p->periodic_reserved[1] || p->periodic_reserved[2])
+        return fail(SPHB_ERR_INVALID, "sphb_params.periodic_reserved must be 0: periodic boxes are set up through sphb_slab (sphb_mg_pack)");
     if (p->cell_x_div < 0 || p->cell_x_div > 64) return fail(SPHB_ERR_INVALID, "cell_x_div must be in [0, 64]");
     if (p->domain_mode == SPHB_DOMAIN_FIXED)
         for (int a = 0; a < 3; a++)
@@ -374,6 +376,8 @@ int sphb_create(const sphb_params* p, int device, sphb_engine** out) {
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_grid, sizeof(GridDesc));
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_bbox, sizeof(BBoxAcc));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_stats, 4 * sizeof(unsigned int));
+    if (err == cudaSuccess) err = cudaMemsetAsync(e->d_stats, 0, 4 * sizeof(unsigned int), e->stream);
     if (err != cudaSuccess) {
         sphb_destroy(e);
         return fail(SPHB_ERR_CUDA, "engine setup failed: %s", cudaGetErrorString(err));
@@ -395,6 +399,7 @@ void sphb_destroy(sphb_engine* e) {
     if (e->d_spheres) cudaFree(e->d_spheres);
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
+    if (e->d_stats) cudaFree(e->d_stats);
     if (e->ev) {
         for (int i = 0; i < 4 * sphb_engine::kMaxTimed; i++) cudaEventDestroy(e->ev[i]);
         delete[] e->ev;
@@ -500,8 +505,26 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
         CK(cudaMemcpyAsync(e->vel[0].p, vel, n * sizeof(float4), cudaMemcpyDeviceToDevice, e->stream));
         CK(cudaMemsetAsync(e->aux[0].p, 0, n * sizeof(float4), e->stream));
         CK(cudaMemsetAsync(e->accel[0].p, 0, n * sizeof(float4), e->stream));
-        if (ids) CK(cudaMemcpyAsync(e->oid[0].p, ids, n * sizeof(int), cudaMemcpyDeviceToDevice, e->stream));
-        else LAUNCH(e, k_fill_iota, cdiv(n, 256), 256, 0, e->oid[0].p, (int)n);
+        if (ids) {
+            // the ids index the inverse permutation and order the stable rank: anything but a permutation of 0..n-1 would
+            // write out of bounds or lose particles later, so it is refused here (one extra pass and a synchronisation,
+            // only on this id-carrying path)
+            CK(e->scratch.reserve(4));
+            unsigned int* d_bad = (unsigned int*)e->scratch.p;
+            CK(cudaMemsetAsync(d_bad, 0, sizeof(unsigned int), e->stream));
+            CK(cudaMemsetAsync(e->inv.p, 0xff, n * sizeof(int), e->stream));
+            LAUNCH(e, k_check_ids, cdiv(n, 256), 256, 0, ids, (int)n, e->inv.p, d_bad);
+            CK(cudaGetLastError());
+            unsigned int h_bad = 0;
+            CK(cudaMemcpyAsync(&h_bad, d_bad, sizeof h_bad, cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaStreamSynchronize(e->stream));
+            if (h_bad) {
+                e->have_state = false;
+                return fail(SPHB_ERR_INVALID, "ids must be a permutation of 0..n-1: %u of %zu are out of range or repeated", h_bad, n);
+            }
+            CK(cudaMemcpyAsync(e->oid[0].p, ids, n * sizeof(int), cudaMemcpyDeviceToDevice, e->stream));
+        } else
+            LAUNCH(e, k_fill_iota, cdiv(n, 256), 256, 0, e->oid[0].p, (int)n);
         CK(cudaGetLastError());
     }
     e->have_state = true;
@@ -746,6 +769,7 @@ int sphb_step(sphb_engine* e, int nsteps) {
             CK(cudaEventRecord(ev[3], e->stream));
             e->timed_steps++;
         }
+        e->steps_done++;
     }
     return SPHB_OK;
 }
@@ -898,6 +922,22 @@ int sphb_get_timing(sphb_engine* e, float ms[4], int* steps) {
 }
 
 uint64_t sphb_launch_count(const sphb_engine* e) { return e ? e->launches : 0; }
+
+int sphb_get_stats(sphb_engine* e, sphb_stats* out) {
+    if (!e || !out) return fail(SPHB_ERR_INVALID, "null argument");
+    int rc = use_device(e);
+    if (rc) return rc;
+    unsigned int h[4] = {0, 0, 0, 0};
+    CK(cudaMemcpyAsync(h, e->d_stats, sizeof h, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    memset(out, 0, sizeof *out);
+    out->arrival_order_cells = h[0];
+    out->steps = e->steps_done;
+    out->launches = e->launches;
+    out->particles = e->n;
+    out->capacity = e->posm[0].cap;
+    return SPHB_OK;
+}
 
 int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, void** accel, int32_t** ids) {
     int rc = check_ready(e);

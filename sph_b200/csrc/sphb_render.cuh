@@ -100,4 +100,13 @@ __global__ void __launch_bounds__(256) k_fill_iota(int* __restrict__ ids, int n)
     if (i < n) ids[i] = i;
 }
 
+// Caller-supplied particle ids must be a permutation of 0..n-1: the downloads invert them (k_invert_perm) and the
+// stable rank orders cells by them.  seen[] must be filled with -1; bad[0] counts ids out of range or used twice.
+__global__ void __launch_bounds__(256) k_check_ids(const int* __restrict__ ids, int n, int* __restrict__ seen, unsigned int* __restrict__ bad) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int id = ids[i];
+    if (id < 0 || id >= n || atomicExch(seen + id, i) != -1) atomicAdd(bad, 1u);
+}
+
 } // namespace sphb

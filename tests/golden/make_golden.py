@@ -33,6 +33,11 @@ def main():
     ref = Reference()
     orc = Oracle()
 
+    # --- the viewer's camera matrix (main.cpp:48-60) from the reference's vendored GLM
+    np.savez_compressed(os.path.join(OUT, "camera.npz"), mvp=ref.default_mvp())
+    if "--only-camera" in sys.argv:
+        return
+
     # --- kernels
     rng = np.random.default_rng(7)
     xi = rng.uniform(-1, 1, (256, 3)).astype(np.float32)

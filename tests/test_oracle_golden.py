@@ -73,3 +73,15 @@ def test_fp64_referee_brackets_the_reference_rounding(oracle, golden):
     assert np.all(scale >= 1.0)
     assert np.max(d / scale) <= 1e-6
     assert np.max(d / np.linalg.norm(a64, axis=1)) <= 5e-5
+
+
+def test_camera_matrix_matches_the_references_glm(oracle, golden):
+    """Row f2, the part of it the reference pins: MVP = perspective(45, 4/3, 0.1, 100) * lookAt(...) * I of main.cpp:48-60,
+    as computed by the reference's vendored GLM 0.9.6.1 (tests/golden/camera.npz, from oracle/_ref).  Both the oracle's
+    restatement and the library's sphb_default_camera (host arithmetic, no GPU involved) reproduce it bit for bit."""
+    import sph_b200
+    want = golden("camera.npz")["mvp"]
+    assert np.array_equal(oracle.default_mvp(), want)
+    cam = sph_b200.capi.default_camera()
+    assert np.array_equal(np.array(cam.mvp[:], np.float32), want)
+    assert (cam.width, cam.height) == (1080, 920)       # main.cpp:13-14

@@ -127,3 +127,7 @@ def test_dead_viscosity_forces_pair_body(oracle, reference):
     oracle.viscosity_forces(c, cells=True, threads=2)
     assert same_bits(a, b) and same_bits(a, c)
     assert np.abs(a["accel"] - ps["accel"]).max() > 0.05
+
+
+def test_camera_golden_is_what_the_reference_glm_computes(reference, golden):
+    assert np.array_equal(reference.default_mvp(), golden("camera.npz")["mvp"])

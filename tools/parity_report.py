@@ -104,7 +104,7 @@ def main():
     print("\n| config | rho: ours-ref | rho: ref-f64 | accel plain max / p99.9 / #>1e-5 (ours-ref) | (ref-f64) | (ours-f64) | accel normalised max ours-ref / ref-f64 / ours-f64 |")
     print("|---|---|---|---|---|---|---|")
     for r in rows:
-        f = lambda k: "{max:.1e} / {p99.9:.1e} / {above_1e-5}".format(**r[k]["plain"])
+        f = lambda k: "%.1e / %.1e / %d" % (r[k]["plain"]["max"], r[k]["plain"]["p99.9"], r[k]["plain"]["above_1e-5"])
         print(f"| {r['config']} | {r['density']['ours_vs_ref']:.1e} | {r['density']['ref_vs_f64']:.1e} | {f('accel_ours_vs_ref')} | {f('accel_ref_vs_f64')} | "
               f"{f('accel_ours_vs_f64')} | {r['accel_ours_vs_ref']['normalised_max']:.1e} / {r['accel_ref_vs_f64']['normalised_max']:.1e} / {r['accel_ours_vs_f64']['normalised_max']:.1e} |")
 
