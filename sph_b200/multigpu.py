@@ -199,52 +199,62 @@ def exchange_in_process(ranks, periodic=False):
 
 
 # ---------------------------------------------------------------------------------------------------------
-# bench.py --gpus N (launched under torchrun): weak scaling, one block-drop tank section per GPU
+# bench.py --gpus N (launched under torchrun)
 
-def bench_main(args, world, rank, local):
-    import json
-    import time
+class _Solo:
+    """world size 1: no process group; the only "collectives" are identities."""
+    P2POp = isend = irecv = batch_isend_irecv = None
 
-    import torch
-    import torch.distributed as dist
+    class ReduceOp:
+        MAX = SUM = None
 
-    import bench as B
+    @staticmethod
+    def is_initialized(): return False
+    @staticmethod
+    def get_rank(): return 0
+    @staticmethod
+    def barrier(): pass
+    @staticmethod
+    def all_reduce(t, op=None): return t
+    @staticmethod
+    def broadcast(t, src=0): return t
+    @staticmethod
+    def gather_object(obj, object_gather_list=None, dst=0):
+        if object_gather_list is not None:
+            object_gather_list[0] = obj
+
+
+SCALE_OF = {"drop16m": 1, "drop2m": 2, "drop256k": 4, "periodic16m": 1, "periodic2m": 2, "periodic256k": 4}
+
+
+def setup_slab_run(mode, scale, world, rank, local, accel=True):
+    """One rank's share of a slab-decomposed workload: (engine, SlabRank, own host records, neighbours, description).
+    mode: "sections" = config-4 pattern, one tank section per GPU (weak); "strong" = the ONE config-4 tank cut into `world`
+    slabs of equal owned-plus-ghost counts; "periodic" = config 5, a fully periodic box per GPU, `world` side by side in x."""
     from . import scenes
-
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     R = support_radius()
     halo = 2.0 * R * 1.001
-    periodic = args.workload.startswith("periodic")
-    if periodic:
-        # config 5: 256^3/scale^3 particles per GPU in a fully periodic box, G boxes side by side in x; no gravity, no walls
-        scale = {"periodic16m": 1, "periodic2m": 2, "periodic256k": 4}[args.workload]
+    if mode == "periodic":
         side = 256 // scale
         L = side * 0.1
         pos, vel = scenes.lattice_block(side, side, side, 0.1, (0.05 + L * rank, 0.05, 0.05), seed=1234 + rank, jitter=0.2, vel_amp=0.5)
         ps = scenes.make_particles(pos, vel)
         del pos, vel
-        walls = None
         bounds = [L * r for r in range(world + 1)]
         slab = make_slab(rank, world, bounds, halo, period=L * world, yz_box=((0.0, L), (0.0, L)))
         left, right = neighbours(rank, world, periodic=True)
         m = halo + 0.35
         dlo, dhi = (bounds[rank] - m, -m, -m), (bounds[rank + 1] + m, L + m, L + m)
         eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi, gravity=(0.0, 0.0, 0.0),
-                          write_accel=0 if args.no_accel else 1)
+                          write_accel=1 if accel else 0)
         n_own = len(ps)
         capacity = int((L + 2 * halo) ** 2 * 1100.0 * halo * 1.6) + 4096
         eng.reserve(int(n_own * ((L + 2 * halo) / L) ** 3 * 1.08) * 2 - n_own + 4 * capacity)   # old ghosts stay (dead) until the next sort
-        what = f", periodic box {L:.1f}^3 per GPU ({world} side by side in x), gravity off, no walls"
+        what = f"weak-scaling periodic box {L:.1f}^3 of {n_own} particles per GPU ({world} side by side in x), gravity off, no walls (config 5)"
     else:
-        scale = {"drop16m": 1, "drop2m": 2, "drop256k": 4}.get(args.workload)
-        if scale is None:
-            raise SystemExit("multi-GPU bench runs the block-drop (drop16m / drop2m / drop256k) and periodic workloads")
         section = 256 // scale * 0.1                     # x-length of one tank section
-        strong = getattr(args, "scaling", "weak") == "strong"
+        strong = mode == "strong"
         if strong:
-            # config 4 as written: ONE tank, N slabs whose boundaries sit at particle-count quantiles of x
             ps, walls = scenes.block_drop(scale=scale)
             bounds = balanced_bounds(ps["pos"][:, 0], world, R, 0.0, section + 0.2, halo)
             ps = ps[(ps["pos"][:, 0] >= (bounds[rank] if rank else -1e30)) & (ps["pos"][:, 0] < (bounds[rank + 1] if rank < world - 1 else 1e30))].copy()
@@ -258,70 +268,68 @@ def bench_main(args, world, rank, local):
         top = 0.1 + (192 + 256) // scale * 0.1 + 0.3 + 1.0
         dlo = (bounds[rank] - halo - 0.35, -0.25, -0.25)
         dhi = (bounds[rank + 1] + halo + 0.35, top, section + 0.45)
-        eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi,
-                          write_accel=0 if args.no_accel else 1)
+        eng = capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=dlo, domain_hi=dhi, write_accel=1 if accel else 0)
         eng.set_walls(walls)
         column = (192 + (256 if strong else 0)) // scale * 0.1 + 0.5        # a strong-scaling cut may pass through the falling block
         face = (section + 0.2) * column * 1100.0                             # particles per unit x near a face (upper bound)
         capacity = int(face * halo * 2.0) + 4096
         eng.reserve(n_own + 4 * capacity)   # last step's ghosts stay (marked dead) until the next sort drops them
-        what = (f", ONE tank cut into {world} x-slabs of equal owned-plus-ghost particle counts" if strong
-                else f", one tank section per GPU ({world} sections side by side)")
+        what = (f"block drop into tank (config 4), ONE tank of {2 ** 24 // scale ** 3} particles cut into {world} x-slabs of equal owned-plus-ghost counts" if strong
+                else f"block drop into tank (config 4 pattern), one tank section of {n_own} particles per GPU ({world} sections side by side)")
     sr = SlabRank(eng, slab, capacity, local)
+    return eng, sr, ps, (left, right), what, capacity
 
-    class _Solo:  # world size 1: no process group; the only "collectives" are identities
-        ReduceOp = dist.ReduceOp
-        P2POp, isend, irecv, batch_isend_irecv = dist.P2POp, dist.isend, dist.irecv, dist.batch_isend_irecv
-        @staticmethod
-        def is_initialized(): return False
-        @staticmethod
-        def get_rank(): return 0
-        @staticmethod
-        def barrier(): pass
-        @staticmethod
-        def all_reduce(t, op=None): return t
-        @staticmethod
-        def destroy_process_group(): pass
-    if world == 1:
-        dist = _Solo
 
+def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup, e2e_steps=0, sample_clocks=False, reset_every=16):
+    """Times `steps` slab-decomposed steps (pack -> exchange -> unpack -> engine step) after `warmup`: CUDA events on the engine's
+    stream between two barriers + synchronisations, max over ranks.  Returns a dict; every rank gets the same timing values."""
+    import time
+
+    import torch
+
+    import bench as B
+
+    accel = not args.no_accel
+    eng, sr, ps, (left, right), what, capacity = setup_slab_run(mode, scale, world, rank, local, accel)
+    n_own = len(ps)
     host = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
     host_np = host.numpy().view(capi.PARTICLE)
     host_np[:] = ps
     del ps
     eng.upload(host_np)
-
     eng.update_cells()
     init = [torch.from_numpy(a).cuda() for a in eng.download_soa()[:2]]   # this rank's initial owned state, on the device
     init[1][:, 3] = 1.0
     since_reset = [0]
+    xdist = dist      # world size 1: the _Solo shim (a lone rank in a periodic box is its own neighbour and copies locally)
 
     def one_step():
         # the reference's scheme blows up on deep pools after ~35 steps (bench.py --reset-every): start over in time
-        if args.reset_every > 0 and since_reset[0] >= args.reset_every:
+        if reset_every > 0 and since_reset[0] >= reset_every:
             eng.upload_soa_device(init[0].data_ptr(), init[1].data_ptr(), n_own)
             since_reset[0] = 0
-        sr.step(dist, left, right)
+        sr.step(xdist, left, right)
         since_reset[0] += 1
 
-    for _ in range(max(3, args.warmup)):
+    for _ in range(max(3, warmup)):
         one_step()
     eng.synchronize()
     launches0 = eng.launch_count()
     eng.enable_timing(True)
-    sampler = B.ClockSampler(local) if rank == 0 else None
+    sampler = B.ClockSampler(local) if (sample_clocks and rank == 0) else None
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     dist.barrier()
     torch.cuda.synchronize()
     start.record(sr.stream)
-    for _ in range(args.steps):
+    for _ in range(steps):
         one_step()
     stop.record(sr.stream)
     eng.synchronize()
     torch.cuda.synchronize()
     dist.barrier()
     ms = torch.tensor([start.elapsed_time(stop)], device="cuda")
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     clocks = sampler.stop() if sampler else None
     launches = eng.launch_count() - launches0
@@ -330,13 +338,14 @@ def bench_main(args, world, rank, local):
     bad = eng.count_nonfinite()
     assert bad == 0, f"rank {rank}: {bad} non-finite particles after the timed steps"
     _, vel = sr.owned()
-    owned = torch.tensor([len(vel)], device="cuda", dtype=torch.int64)
-    dist.all_reduce(owned)
-    total = int(owned.item())
-    expect = torch.tensor([n_own], device="cuda", dtype=torch.int64)
-    dist.all_reduce(expect)
-    assert total == int(expect.item()), f"particles lost or duplicated by the exchange: {total} owned, {int(expect.item())} generated"
-    value = total * args.steps / (ms * 1e-3)
+    cnt = torch.tensor([len(vel), n_own, int(launches)], device="cuda", dtype=torch.int64)
+    step_max = torch.tensor([float(phase[3])], device="cuda")
+    if world > 1:
+        dist.all_reduce(cnt)
+        dist.all_reduce(step_max, op=dist.ReduceOp.MAX)
+    total, expect, launches_all = (int(x) for x in cnt.tolist())
+    assert total == expect, f"particles lost or duplicated by the exchange: {total} owned, {expect} generated"
+    value = total * steps / (ms * 1e-3)
 
     # where the time between two engine steps goes (a few extra steps, events on the engine's stream; not part of `value`)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
@@ -346,9 +355,9 @@ def bench_main(args, world, rank, local):
         ev[0].record(sr.stream)
         sr.pack()
         ev[1].record(sr.stream)
-        sr.exchange_distributed(dist, left, right)
+        sr.exchange_distributed(xdist, left, right)
         ev[2].record(sr.stream)
-        sr.unpack()                      # synchronises (reads the counts)
+        sr.unpack()
         ev[3].record(sr.stream)
         eng.step(1)
         since_reset[0] += 1
@@ -356,55 +365,165 @@ def bench_main(args, world, rank, local):
         parts += [ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])]
     parts /= nb
 
-    # end to end on host records: upload own records, exchange ghosts, step, download own records
-    e2e_steps = max(1, args.e2e_steps)
-    out = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
-    out_np = out.numpy().view(capi.PARTICLE)
+    out = {"workload": what, "particles": total, "particles_per_gpu_rank0": n_own, "n_gpus": world, "steps": steps, "warmup": max(3, warmup),
+           "ms_per_step": ms / steps, "value": value, "gpu_launches": launches_all,
+           "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "engine_step_rank0": float(phase[3]),
+                        "engine_step_max_over_ranks": float(step_max.item()),
+                        "breakdown_rank0": {"pack": float(parts[0]), "send_recv": float(parts[1]), "unpack": float(parts[2])}},
+           "exchange_exposed_ms": ms / steps - float(step_max.item()),
+           "halo": {"counts_rank0": {"kept": sr.counts[0], "from_left": sr.counts[1], "from_right": sr.counts[2]}, "message_capacity": capacity},
+           "local_particles_incl_ghosts_rank0": eng.count(), "clocks": clocks, "_phase": phase}
 
-    def e2e_step():
-        eng.upload(host_np)             # the rank's own 52-byte records (pinned)
-        sr.step(dist, left, right)      # ghosts come from the neighbours
-        eng.download_first(out_np)      # own records back (ghosts are not returned)
+    if e2e_steps:
+        # end to end on host records: upload own records, exchange ghosts, step, download own records
+        res = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
+        res_np = res.numpy().view(capi.PARTICLE)
 
-    e2e_step()
-    dist.barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+        def e2e_step():
+            eng.upload(host_np)             # the rank's own 52-byte records (pinned)
+            sr.step(xdist, left, right)     # ghosts come from the neighbours
+            eng.download_first(res_np)      # own records back (ghosts are not returned)
+
         e2e_step()
-    torch.cuda.synchronize()
-    t = torch.tensor([(time.perf_counter() - t0) / e2e_steps], device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    t_e2e = float(t.item())
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        t = torch.tensor([(time.perf_counter() - t0) / e2e_steps], device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+        out["e2e"] = {"value": total / t_e2e, "unit": B.UNIT, "h2d_bytes_per_step": expect * 52, "d2h_bytes_per_step": expect * 52,
+                      "ms_per_step": 1e3 * t_e2e, "call": "per rank: sphb_upload_aos + halo exchange + sphb_step + sphb_download_aos"}
+    eng.close()
+    del init, host_np, host
+    torch.cuda.empty_cache()
+    return out
 
+
+def parity_vs_single(args, world, rank, local, dist, steps=12, scale=4):
+    """Hardware check of the NCCL path (SURVEY.md 8(e) "Check"): the config-4 scene at 262,144 particles stepped `steps` times through
+    SlabRank.step on all ranks AND through one engine on rank 0; owned particles gathered to rank 0 and paired with the single
+    engine's by position.  Same bounds as tests/test_gpu_multirank.py: positions <= 2e-5, density <= 1e-5 relative."""
+    import torch
+
+    from . import scenes
+    eng, sr, ps, (left, right), _, _ = setup_slab_run("strong", scale, world, rank, local, True)
+    eng.upload(ps)
+    xdist = dist
+    for _ in range(steps):
+        sr.step(xdist, left, right)
+    posm, vel, aux = eng.download_soa()[:3]
+    keep = vel[:, 3] != 0
+    mine = (posm[keep], aux[keep, 0].copy())
+    eng.close()
+    gathered = [None] * world if rank == 0 else None
+    if world > 1:
+        dist.gather_object(mine, gathered, dst=0)
+    else:
+        gathered = [mine]
+    out = None
+    if rank == 0:
+        from scipy.spatial import cKDTree
+        full, walls = scenes.block_drop(scale=scale)
+        section = 256 // scale * 0.1
+        top = 0.1 + (192 + 256) // scale * 0.1 + 0.3 + 1.0
+        with capi.Engine(device=local, domain_mode=capi.DOMAIN_FIXED, domain_lo=(-0.25, -0.25, -0.25), domain_hi=(section + 0.45, top, section + 0.45)) as e1:
+            e1.set_walls(walls)
+            e1.upload(full)
+            e1.step(steps)
+            p1, _, a1 = e1.download_soa()[:3]
+        pm = np.concatenate([g[0] for g in gathered])
+        rm = np.concatenate([g[1] for g in gathered])
+        ok_count = len(pm) == len(p1)
+        d, idx = cKDTree(pm[:, :3].astype(np.float64)).query(p1[:, :3].astype(np.float64))
+        one_to_one = len(np.unique(idx)) == len(p1)
+        drho = np.abs(rm[idx].astype(np.float64) - a1[:, 0]) / a1[:, 0]
+        out = {"particles": int(len(p1)), "steps": steps, "count_conserved": bool(ok_count), "pairing_one_to_one": bool(one_to_one),
+               "compressed_fraction": float((a1[:, 0] > 10.0).mean()),      # > 0: the falling block has hit the pool, pressure forces are active
+               "max_dpos": float(d.max()), "max_drho_rel": float(drho.max()), "bounds": {"max_dpos": 2e-5, "max_drho_rel": 1e-5}}
+        assert ok_count and one_to_one and out["max_dpos"] <= 2e-5 and out["max_drho_rel"] <= 1e-5, f"multi-GPU result differs from the single engine: {out}"
+    torch.cuda.empty_cache()
+    return out
+
+
+def n1_baselines(args, scale, local, rank, dist, steps=8):
+    """Rank 0 alone runs both named configs on ONE GPU (the others wait): the denominators of efficiency_vs_n1."""
+    import bench as B
+    out = None
+    if rank == 0:
+        name = {1: "drop16m", 2: "drop2m", 4: "drop256k"}[scale]
+        r = B.run_resident(name, steps, 3, local, accel=not args.no_accel)
+        p = run_slab_workload(args, "periodic", scale, 1, 0, local, _Solo, steps, 3)
+        out = {"config4_ms_per_step": r["ms_per_step"], "config4_value": r["value"], "config5_ms_per_step": p["ms_per_step"], "config5_value": p["value"]}
+    dist.barrier()
+    return out
+
+
+def strip(d):
+    return {k: v for k, v in d.items() if not k.startswith("_")}
+
+
+def bench_main(args, world, rank, local):
+    import json
+
+    import torch
+    import torch.distributed as tdist
+
+    import bench as B
+
+    torch.cuda.set_device(local)
+    dist = _Solo
+    if world > 1:
+        tdist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = tdist
+    periodic = args.workload.startswith("periodic")
+    scale = SCALE_OF.get(args.workload)
+    if scale is None:
+        raise SystemExit("multi-GPU bench runs the block-drop (drop16m / drop2m / drop256k) and periodic workloads")
+    mode = "periodic" if periodic else ("strong" if getattr(args, "scaling", "weak") == "strong" else "sections")
+    reset = args.reset_every if args.reset_every is not None else 16
+    head = run_slab_workload(args, mode, scale, world, rank, local, dist, args.steps, args.warmup, e2e_steps=max(1, args.e2e_steps),
+                             sample_clocks=True, reset_every=reset)
+    sub = {}
+    if not getattr(args, "quick", False):
+        k = max(4, min(args.steps, 10))
+        n1 = n1_baselines(args, scale, local, rank, dist) if world > 1 else None
+        for key, m in (("config4_strong", "strong"), ("config5_periodic", "periodic")):
+            if m == mode:
+                r = head
+            else:
+                r = run_slab_workload(args, m, scale, world, rank, local, dist, k, 3, reset_every=reset)
+            rec = strip(r)
+            rec["scaling"] = "strong" if m == "strong" else "weak"
+            if n1 is not None:
+                base = n1["config4_value"] if m == "strong" else n1["config5_value"]
+                rec["n1_value_same_run_rank0"] = base
+                rec["efficiency_vs_n1"] = r["value"] / (world * base)   # aggregate throughput over N x the one-GPU throughput (weak and strong alike)
+            sub[key] = rec
+        sub["parity_vs_single"] = parity_vs_single(args, world, rank, local, dist)
     if rank == 0:
         peak, peak_src = B.measured_peak()
-        bforce = B.B_FORCE_NOACC if args.no_accel else B.B_FORCE
-        n_local = eng.count()
-        ach = bforce * n_local / (float(phase[2]) * 1e-3) / 1e9
+        phase = head["_phase"]
+        n_local = head["local_particles_incl_ghosts_rank0"]
+        rl = B.rooflines(n_local, phase, not args.no_accel, head["clocks"].get("sm_mhz") if head["clocks"] else None)
+        rl["roofline"]["kernel"] = "k_force (rank 0, local particles incl. ghosts)"
         line = {
-            "metric": B.METRIC, "value": value, "unit": B.UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": getattr(args, "scaling", "weak"), "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": B.WORKLOADS[args.workload] + what,
-                       "particles": total, "particles_per_gpu": n_own, "decomposition": "x slabs, halo = 2 support radii, "
-                       "one NCCL send/recv pair per neighbour per step", "l2": "state exceeds the 126 MB L2",
-                       "accel_output": not args.no_accel},
-            "clocks": clocks,
-            "e2e": {"value": total / t_e2e, "unit": B.UNIT, "h2d_bytes_per_step": n_own * 52 * world, "d2h_bytes_per_step": n_own * 52 * world,
-                    "ms_per_step": 1e3 * t_e2e, "call": "per rank: sphb_upload_aos + halo exchange + sphb_step + sphb_download_aos"},
-            "gpu_launches": int(launches) * world,
-            "roofline": {"bound": "hbm", "kernel": "k_force (rank 0)", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": peak_src, "bytes_per_particle": bforce, "kernel_ms": float(phase[2]),
-                         "local_particles_incl_ghosts": n_local, "steps_averaged": int(timed)},
-            "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "engine_step": float(phase[3]),
-                         "exchange_and_pack": ms / args.steps - float(phase[3]),
-                         "breakdown_rank0": {"pack": float(parts[0]), "send_recv": float(parts[1]), "unpack": float(parts[2])}},
-            "halo": {"counts_rank0": {"kept": sr.counts[0], "from_left": sr.counts[1], "from_right": sr.counts[2]},
-                     "message_capacity": capacity},
+            "metric": B.METRIC, "value": head["value"], "unit": B.UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong" if mode == "strong" else "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": head["workload"], "particles": head["particles"], "particles_per_gpu": head["particles_per_gpu_rank0"],
+                       "decomposition": "x slabs, halo = 2 support radii, one NCCL send/recv pair per neighbour per step",
+                       "l2": "state exceeds the 126 MB L2", "accel_output": not args.no_accel, "reset_every": reset},
+            "clocks": head["clocks"], "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
+            "phase_ms": head["phase_ms"], "exchange_exposed_ms": head["exchange_exposed_ms"], "halo": head["halo"],
             "cpu_baseline": None,
         }
+        line.update(rl)
+        line.update(sub)
         print(json.dumps(line, default=float), flush=True)
-    eng.close()
     dist.barrier()
-    dist.destroy_process_group()
+    if world > 1:
+        tdist.destroy_process_group()

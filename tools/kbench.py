@@ -34,7 +34,7 @@ def child(args):
     eng.update_cells()
     init = [torch.from_numpy(a).cuda() for a in eng.download_soa()[:2]]
     init[1][:, 3] = 1.0
-    reset = 8 if args.workload == "dam64k" else 16
+    reset = 4 if args.workload == "dam64k" else 16
     since = 0
 
     def step():
