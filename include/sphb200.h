@@ -287,8 +287,23 @@ int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* msg_left, s
  * set.  Synchronises once to read the counts.  counts[4] (may be NULL) = {records before the messages (the dropped
  * ones stay in the arrays, marked dead with mass -1, until the next step's sort removes them -- reserve room for
  * them), from_left, from_right, total}.  sphb_count() excludes the dead again after the next step.
- * SPHB_ERR_CAPACITY if a sender overflowed its message or the arrays reserved with sphb_reserve are full. */
+ * SPHB_ERR_CAPACITY if a sender overflowed its message or the arrays reserved with sphb_reserve are full; that is final (the
+ * senders have already given the particles up): the engine drops its state and must be uploaded again. */
 int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, size_t counts[4]);
+
+/* The same without waiting for the GPU: nothing is read back, so the host can enqueue the next step at once and the GPU never
+ * idles between steps.  Until some call needs the exact count (sphb_count, downloads, ... -- they synchronise and fetch it),
+ * the engine works with an ESTIMATE of its particle count for sizing launches while its kernels read the real count from
+ * device memory.  The verdict of the exchange -- its counts, and whether a message or the arrays overflowed -- arrives one call
+ * late: sphb_mg_poll returns it, and the next sphb_mg_pack reports an overflow as SPHB_ERR_CAPACITY.  An overflow is final
+ * either way (the senders have already given the particles up): the engine drops its state and must be uploaded again. */
+int sphb_mg_unpack_async(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right);
+
+/* Status of the latest sphb_mg_unpack_async whose result has reached the host: status[0..6] = {records before the messages,
+ * from_left, from_right, total, dead among them, sent left, sent right}, status[7] = how many asynchronous unpacks have reported so
+ * far.  wait != 0 blocks until the latest one has (its event sits before the kernels of the following step, so this does not
+ * drain the GPU); wait == 0 returns the newest record available.  SPHB_ERR_CAPACITY if that exchange overflowed. */
+int sphb_mg_poll(sphb_engine* e, size_t status[8], int wait);
 
 /* Records the last sphb_mg_pack wanted to put into its left / right message (known once sphb_mg_unpack has read the
  * counts back).  Both ends of a link see the same number -- the sender here, the receiver in counts[1] / counts[2] --

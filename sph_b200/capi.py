@@ -76,7 +76,7 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats",
+    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats", "sphb_mg_unpack_async", "sphb_mg_poll",
 ]
 
 _lib = None
@@ -144,6 +144,8 @@ def load_library() -> C.CDLL:
     L.sphb_mg_sent.argtypes = [vp, C.POINTER(sz * 2)]
     L.sphb_mg_pack_limits.argtypes = [vp, C.POINTER(Slab), vp, sz, vp, sz]
     L.sphb_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.sphb_mg_unpack_async.argtypes = [vp, C.POINTER(Slab), vp, vp]
+    L.sphb_mg_poll.argtypes = [vp, C.POINTER(sz * 8), i32]
     _lib = L
     return L
 
@@ -293,6 +295,16 @@ class Engine:
         self._check(self.lib.sphb_mg_unpack(self.h, C.byref(slab), C.c_void_p(from_left) if from_left else None,
                                             C.c_void_p(from_right) if from_right else None, C.byref(counts)))
         return tuple(int(c) for c in counts)
+
+    def mg_unpack_async(self, slab: Slab, from_left: int | None, from_right: int | None):
+        self._check(self.lib.sphb_mg_unpack_async(self.h, C.byref(slab), C.c_void_p(from_left) if from_left else None,
+                                                  C.c_void_p(from_right) if from_right else None))
+
+    def mg_poll(self, wait: bool = True):
+        """(kept, from_left, from_right, total, dead, sent_left, sent_right, reports so far) of the latest asynchronous unpack."""
+        st = (C.c_size_t * 8)()
+        self._check(self.lib.sphb_mg_poll(self.h, C.byref(st), int(wait)))
+        return tuple(int(x) for x in st)
 
     def mg_sent(self):
         sent = (C.c_size_t * 2)()

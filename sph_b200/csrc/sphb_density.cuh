@@ -12,10 +12,10 @@ namespace sphb {
 // i.e. exactly what a CPU stable counting sort of the uploaded order produces) and moves the state.
 
 __global__ void __launch_bounds__(256) k_scatter(const int* __restrict__ key, const int* __restrict__ slot, const int* __restrict__ oid,
-                                                 const int* __restrict__ cell_start, int2* __restrict__ pairs, int n) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    pairs[cell_start[key[i]] + slot[i]] = make_int2(oid ? oid[i] : i, i); // oid == nullptr: ids are the slot numbers
+                                                 const int* __restrict__ cell_start, int2* __restrict__ pairs, int n, const int* __restrict__ n_dev) {
+    if (n_dev) n = *n_dev; // the count lives on the device (sphb_mg_unpack_async); the launch was sized from an estimate
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        pairs[cell_start[key[i]] + slot[i]] = make_int2(oid ? oid[i] : i, i); // oid == nullptr: ids are the slot numbers
 }
 
 // A cell that holds more than this many particles (a clamped boundary cell full of strays, or everything gone
@@ -37,11 +37,12 @@ __global__ void __launch_bounds__(256) k_rank_gather(const int2* __restrict__ pa
                                                      const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                      float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                      float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                     int* __restrict__ oid_out, int n, const GridDesc* __restrict__ gd,
-                                                     unsigned int* __restrict__ stats) {
-    int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, gd->ncell, stats);
+                                                     int* __restrict__ oid_out, int n, const int* __restrict__ n_dev,
+                                                     const GridDesc* __restrict__ gd, unsigned int* __restrict__ stats) {
+    if (n_dev) n = *n_dev;
+    const int ncell = gd->ncell;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x)
+        rank_gather_one<kCarryAll>(p, pairs, key, cell_start, posm_in, vel_in, aux_in, acc_in, posm_out, vel_out, aux_out, acc_out, oid_out, ncell, stats);
 }
 
 template <bool kCarryAll>
@@ -127,7 +128,10 @@ constexpr int kDT = 4;
 constexpr int kRgThreads = 1024;
 
 // the work of one block of kRgThreads threads (k_row_groups, and one phase of k_sort_small)
-__device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* cell_start, int* gstart) {
+__device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* cell_start, int* gstart, int* counts) {
+    // counts[1] = particles in real cells = the live count after this sort (records filed in the trash bins excluded):
+    // what the kernels after the sort use as n when the host does not know it (sphb_mg_unpack_async)
+    if (threadIdx.x == 0 && counts) counts[1] = cell_start[nx * nrows];
     __shared__ int s_warp[kRgThreads / 32];
     __shared__ int s_carry;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -166,8 +170,8 @@ __device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* c
 }
 
 __global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
-                                                          int* __restrict__ gstart) {
-    row_groups_block(gd->dims[0], gd->dims[1] * gd->dims[2], cell_start, gstart);
+                                                          int* __restrict__ gstart, int* __restrict__ counts) {
+    row_groups_block(gd->dims[0], gd->dims[1] * gd->dims[2], cell_start, gstart, counts);
 }
 
 // The row rho with gstart[rho] <= t < gstart[rho + 1] (t = density-group index).  One 32-ary search per WARP
@@ -207,7 +211,7 @@ __device__ __forceinline__ int find_row(const int* __restrict__ gstart, int nrow
 // words of row r.
 template <bool kAux, bool kMask>
 __device__ __forceinline__ void density_row_single(const Consts& c, const float4* __restrict__ posm, unsigned int* __restrict__ mask,
-                                                   int n, int i, const float4& pi, int r, int jb, int je, float& sum) {
+                                                   int mstride, int i, const float4& pi, int r, int jb, int je, float& sum) {
     const int jm = min(je, jb + kMaskBits);
     unsigned int m0 = 0, m1 = 0; // bits enter at the top and slide down: after len steps bit k = candidate k
     int j = jb;
@@ -240,8 +244,8 @@ __device__ __forceinline__ void density_row_single(const Consts& c, const float4
             if (self < 32) m0 &= ~(1u << self);
             else if (self < kMaskBits) m1 &= ~(1u << (self - 32));
         }
-        mask[(size_t)(2 * r) * n + i] = m0;      // word w of row r covers candidates jb + 32*w ...
-        mask[(size_t)(2 * r + 1) * n + i] = m1;
+        mask[(size_t)(2 * r) * mstride + i] = m0;      // word w of row r covers candidates jb + 32*w ...
+        mask[(size_t)(2 * r + 1) * mstride + i] = m1;
     }
 }
 
@@ -269,17 +273,14 @@ __device__ __forceinline__ void density_row_single(const Consts& c, const float4
 // kLanes: 1, or 16 for small scenes: the 9 rows of a group go to 9 of 16 consecutive lanes (partial sums joined by
 // shuffles, each lane writes its own row's mask words), because with a few hundred groups the GPU is empty and what
 // counts is the length of one thread's chain: 972 particles (main.cpp's scene) 30 us -> see DESIGN.md.
-template <bool kAux, bool kMask, int kLanes = 1>
-__global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
-                                                 const int* __restrict__ gstart,
-                                                 const float4* __restrict__ posm, const float4* __restrict__ vel,
-                                                 float4* __restrict__ aux, float4* __restrict__ vr,
-                                                 unsigned int* __restrict__ mask, int n) {
-    const GridDesc g = *gd;
-    const int tg = blockIdx.x * blockDim.x + threadIdx.x;
+template <bool kAux, bool kMask, int kLanes>
+__device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& g, const int* __restrict__ cell_start,
+                                               const int* __restrict__ gstart,
+                                               const float4* __restrict__ posm, const float4* __restrict__ vel,
+                                               float4* __restrict__ aux, float4* __restrict__ vr,
+                                               unsigned int* __restrict__ mask, const int n /* mask stride */, const int tg,
+                                               const int nrows_grid, const int ngroups) {
     const int t_raw = tg / kLanes, sub = tg % kLanes; // group, and which of its rows this lane takes (kLanes > 1)
-    const int nrows_grid = g.dims[1] * g.dims[2];
-    const int ngroups = __ldg(gstart + nrows_grid);
     if ((tg & ~31) / kLanes >= ngroups) return;    // whole warp beyond the last group
     const bool live = t_raw < ngroups;
     const int t = live ? t_raw : ngroups - 1;       // spare lanes of the last warp shadow the last group (warp-wide votes below)
@@ -451,6 +452,29 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
     }
 }
 
+// The kernel: thread tg takes group tg (of kLanes lanes); the group total is read from the device.  n = stride of the mask
+// rows (a capacity, not the particle count).  When the host only has an ESTIMATE of the particle count
+// (sphb_mg_unpack_async) the main launch (kLoop = false) covers the estimate and a small second launch with kLoop = true,
+// first = threads of the main launch, walks whatever lies beyond in grid strides -- normally nothing.  (One launch that
+// always loops cost 12 % here: the loop-carried state pushes the 64-register kernel into more spills.)
+template <bool kAux, bool kMask, int kLanes = 1, bool kLoop = false>
+__global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                                 const int* __restrict__ gstart,
+                                                 const float4* __restrict__ posm, const float4* __restrict__ vel,
+                                                 float4* __restrict__ aux, float4* __restrict__ vr,
+                                                 unsigned int* __restrict__ mask, int n, int first) {
+    const GridDesc g = *gd;
+    const int nrows_grid = g.dims[1] * g.dims[2];
+    const int ngroups = __ldg(gstart + nrows_grid);
+    if (!kLoop) {
+        density_thread<kAux, kMask, kLanes>(c, g, cell_start, gstart, posm, vel, aux, vr, mask, n, first + blockIdx.x * blockDim.x + threadIdx.x, nrows_grid, ngroups);
+    } else {
+        const long long nthreads = (long long)ngroups * kLanes;
+        for (long long base = first + (long long)blockIdx.x * blockDim.x; base < nthreads; base += (long long)gridDim.x * blockDim.x)
+            density_thread<kAux, kMask, kLanes>(c, g, cell_start, gstart, posm, vel, aux, vr, mask, n, (int)base + (int)threadIdx.x, nrows_grid, ngroups);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------
 // Small scenes: the whole grid build in ONE launch of one block.  At main.cpp's 972 particles the eight kernels
 // above are eight dependent launches of 3-5 us each for a few hundred nanoseconds of work; here their bodies run
@@ -488,8 +512,9 @@ __global__ void __launch_bounds__(kRgThreads) k_sort_small(Consts c, BBoxAcc* ac
                                                           const float4* __restrict__ aux_in, const float4* __restrict__ acc_in,
                                                           float4* __restrict__ posm_out, float4* __restrict__ vel_out,
                                                           float4* __restrict__ aux_out, float4* __restrict__ acc_out,
-                                                          int* __restrict__ oid_out, int n, int rearm_bbox, int trash,
-                                                          unsigned int* __restrict__ stats) {
+                                                          int* __restrict__ oid_out, int n, const int* __restrict__ n_dev, int* __restrict__ counts,
+                                                          int rearm_bbox, int trash, unsigned int* __restrict__ stats) {
+    if (n_dev) n = *n_dev;
     __shared__ GridDesc s_g;
     __shared__ int s_scan[32];
     const int tid = threadIdx.x;
@@ -524,7 +549,7 @@ __global__ void __launch_bounds__(kRgThreads) k_sort_small(Consts c, BBoxAcc* ac
         carry += tot;
     }
     __syncthreads();
-    row_groups_block(g.dims[0], g.dims[1] * g.dims[2], cell_start, gstart);
+    row_groups_block(g.dims[0], g.dims[1] * g.dims[2], cell_start, gstart, counts);
     for (int i = tid; i < n; i += kRgThreads) pairs[cell_start[key[i]] + slot[i]] = make_int2(oid_in ? oid_in[i] : i, i); // K3
     __syncthreads();
     for (int p = tid; p < n; p += kRgThreads)

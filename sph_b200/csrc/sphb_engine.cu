@@ -86,7 +86,21 @@ struct sphb_engine {
     size_t reserved = 0;
     GridDesc* d_grid = nullptr;
     BBoxAcc* d_bbox = nullptr;
+    DevBuf<float4> warp_box; // per-warp boxes of the new positions, left by the fused force kernel (bbox grid mode)
+    int box_records = 0;     // how many of them the last fused step wrote; 0 = none pending
     unsigned int* d_stats = nullptr; // [0] cells whose stable rank fell back to arrival order (cumulative), [1..3] spare
+    // Particle counts on the device, for the path that never waits for them (sphb_mg_unpack_async):
+    // d_cnt[0] = records in the arrays before the next sort (written by k_mg_commit), d_cnt[1] = live records after the last sort
+    // (written by the sort).  While n_deferred, e->n is only the host's ESTIMATE (launch sizing); kernels read the real count.
+    int* d_cnt = nullptr;
+    int* d_status = nullptr;          // k_mg_commit's status record (8 ints)
+    int* h_status = nullptr;          // pinned, 2 x 8 ints: where the status records land
+    cudaEvent_t ev_status[2] = {nullptr, nullptr};
+    unsigned long long status_issued = 0, status_seen = 0; // async unpacks enqueued / whose status has been read
+    int last_status[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool n_deferred = false;
+    int cnt_slot = 0;                 // which of d_cnt[0] / d_cnt[1] holds the current count
+    size_t mstride = 0;               // stride of the neighbour-mask rows (capacity rounded up to 32)
     uint64_t steps_done = 0;
     long long max_cells = 0;
 
@@ -181,8 +195,10 @@ int ensure_capacity(sphb_engine* e, size_t n) {
     CK(e->inv.reserve(want));
     CK(e->pairs.reserve(want));
     e->rows = (e->c.cell >= e->c.h2) ? 9 : 25;
-    CK(e->mask.reserve(want * (size_t)e->rows * 2));
+    e->mstride = (e->posm[0].cap + 31) & ~(size_t)31; // mask rows 128-byte aligned, and independent of the particle count
+    CK(e->mask.reserve(e->mstride * (size_t)e->rows * 2));
     CK(e->vr.reserve(want));
+    if (!e->c.domain_fixed) CK(e->warp_box.reserve(2 * (e->posm[0].cap / 32 + 4096)));
     if (e->nspheres) CK(e->contacts.reserve(2 * want));
     const int div = e->params.cell_x_div > 0 ? e->params.cell_x_div : 2;
     long long mc = e->params.max_cells > 0 ? e->params.max_cells : (long long)div * (long long)(2 * want + 65536);
@@ -210,6 +226,25 @@ int run_bbox(sphb_engine* e) {
     return SPHB_OK;
 }
 
+// the device-side particle count the kernels should use instead of their n argument (null: the host's n is exact)
+inline const int* n_dev(const sphb_engine* e) { return e->n_deferred ? e->d_cnt + e->cnt_slot : nullptr; }
+
+// d_bbox = box of the current positions: joined from the per-warp boxes of the last fused step if there are any, else one pass
+int ensure_bbox(sphb_engine* e) {
+    if (e->bbox_valid) return SPHB_OK;
+    if (e->box_records > 0) {
+        LAUNCH(e, k_bbox_reset, 1, 32, 0, e->d_bbox);
+        int blocks = cdiv(e->box_records, 256);
+        if (blocks > 148 * 4) blocks = 148 * 4;
+        LAUNCH(e, k_bbox_fold, blocks, 256, 0, e->warp_box.p, e->box_records, e->d_bbox);
+        CK(cudaGetLastError());
+        e->box_records = 0;
+        e->bbox_valid = true;
+        return SPHB_OK;
+    }
+    return run_bbox(e);
+}
+
 constexpr int kSmallSort = 8192; // particles up to which the grid build is one single-block launch
 
 // bookkeeping after either sort path: the new buffer is current, dead records are gone, derived data is stale
@@ -218,18 +253,18 @@ int finish_sort(sphb_engine* e, int nxt) {
     e->oid_identity = false; // the sort wrote the new buffer's ids
     e->n -= e->n_dead; // the dead records now sit behind the live ones: [n, n + n_dead) of the new buffers, never read again
     e->n_dead = 0;
+    e->cnt_slot = 1;   // d_cnt[1] = live count, written by the sort
     e->grid_valid = true;
     e->mask_valid = false;
     e->vr_valid = false;
-    e->bbox_valid = false; // the key pass re-armed the accumulator
     return SPHB_OK;
 }
 
 // K0..K3: grid description, keys, stable counting sort, reorder into the other ping-pong buffer.
 int run_sort(sphb_engine* e, bool carry_all) {
     const int n = (int)e->n;
-    if (!e->c.domain_fixed && !e->bbox_valid) {
-        int rc = run_bbox(e);
+    if (!e->c.domain_fixed) {
+        int rc = ensure_bbox(e);
         if (rc) return rc;
     }
     const int cur = e->cur, nxt = cur ^ 1;
@@ -238,9 +273,10 @@ int run_sort(sphb_engine* e, bool carry_all) {
     if (setup_blocks > 148 * 8) setup_blocks = 148 * 8;
     if (n <= kSmallSort) { // small scene: the eight kernels below as phases of one single-block launch (same functions)
         const int* oid_in = e->oid_identity ? (const int*)nullptr : e->oid[cur].p;
-        const int rearm = e->c.domain_fixed ? 0 : 1, trash = e->n_dead ? 1 : 0;
+        const int rearm = 0, trash = (e->n_dead || e->n_deferred) ? 1 : 0;
 #define SMALL_ARGS e->c, e->d_bbox, e->d_grid, e->cell_start.p, e->row_groups.p, e->key.p, e->slot.p, e->pairs.p, oid_in, e->posm[cur].p, \
-                   e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, rearm, trash, e->d_stats
+                   e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, \
+                   n_dev(e), e->d_cnt, rearm, trash, e->d_stats
         if (carry_all) LAUNCH(e, k_sort_small<true>, 1, kRgThreads, 0, SMALL_ARGS);
         else LAUNCH(e, k_sort_small<false>, 1, kRgThreads, 0, SMALL_ARGS);
 #undef SMALL_ARGS
@@ -249,20 +285,21 @@ int run_sort(sphb_engine* e, bool carry_all) {
     }
     LAUNCH(e, k_grid_setup, setup_blocks, 256, 0, e->c, e->d_bbox, e->d_grid, e->cell_start.p);
     const int pb = cdiv(n, 256);
-    LAUNCH(e, k_key_hist, pb, 256, 0, e->d_grid, e->posm[cur].p, n, e->key.p, e->slot.p, e->cell_start.p, e->d_bbox,
-           e->c.domain_fixed ? 0 : 1, e->n_dead ? 1 : 0);
+    const int* nd = n_dev(e);
+    LAUNCH(e, k_key_hist, pb, 256, 0, e->d_grid, e->posm[cur].p, n, nd, e->key.p, e->slot.p, e->cell_start.p, e->d_bbox,
+           0, (e->n_dead || e->n_deferred) ? 1 : 0);
     LAUNCH(e, k_scan_reduce, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
     LAUNCH(e, k_scan_top, 1, kScanThreads, 0, e->d_grid, e->block_sums.p);
     LAUNCH(e, k_scan_apply, ntile_cap, kScanThreads, 0, e->d_grid, e->cell_start.p, e->block_sums.p);
-    LAUNCH(e, k_row_groups, 1, kRgThreads, 0, e->d_grid, e->cell_start.p, e->row_groups.p);
-    LAUNCH(e, k_scatter, pb, 256, 0, e->key.p, e->slot.p, e->oid_identity ? (const int*)nullptr : e->oid[cur].p, e->cell_start.p, e->pairs.p, n);
+    LAUNCH(e, k_row_groups, 1, kRgThreads, 0, e->d_grid, e->cell_start.p, e->row_groups.p, e->d_cnt);
+    LAUNCH(e, k_scatter, pb, 256, 0, e->key.p, e->slot.p, e->oid_identity ? (const int*)nullptr : e->oid[cur].p, e->cell_start.p, e->pairs.p, n, nd);
     e->oid_identity = false; // k_rank_gather writes the new buffer's ids
     if (carry_all)
         LAUNCH(e, k_rank_gather<true>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid, e->d_stats);
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, nd, e->d_grid, e->d_stats);
     else
         LAUNCH(e, k_rank_gather<false>, pb, 256, 0, e->pairs.p, e->key.p, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, e->d_grid, e->d_stats);
+               e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, nd, e->d_grid, e->d_stats);
     CK(cudaGetLastError());
     return finish_sort(e, nxt);
 }
@@ -277,14 +314,20 @@ int run_density(sphb_engine* e, bool with_aux) {
     long long rows_bound = e->max_cells < kMaxRows ? e->max_cells : kMaxRows;
     if (rows_bound > n) rows_bound = n;
     const long long groups = cdiv(n, kDT) + rows_bound;
-    if (n <= kSmallScene && e->rows == 9) { // small scene: a group's rows side by side on 16 lanes (latency, not throughput)
+    if (n <= kSmallScene && e->rows == 9 && !e->n_deferred) { // small scene: a group's rows side by side on 16 lanes (latency, not throughput)
         auto kfs = with_aux ? k_density<true, true, 16> : k_density<false, true, 16>;
         LAUNCH(e, kfs, cdiv(groups * 16, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
-               e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, n);
+               e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, (int)e->mstride, 0);
     } else {
         auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
-        LAUNCH(e, kfn, cdiv(groups, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
-               e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, n);
+        const int blocks = cdiv(groups, 128);
+        LAUNCH(e, kfn, blocks, 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+               e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, (int)e->mstride, 0);
+        if (e->n_deferred) { // n was an estimate: a few blocks walk whatever groups lie beyond the main launch (normally none)
+            auto ktail = with_aux ? k_density<true, true, 1, true> : k_density<false, true, 1, true>;
+            LAUNCH(e, ktail, 148, 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+                   e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, (int)e->mstride, blocks * 128);
+        }
     }
     CK(cudaGetLastError());
     e->mask_valid = true;
@@ -314,10 +357,57 @@ int run_sphere_collision(sphb_engine* e) {
     return SPHB_OK;
 }
 
-int check_ready(sphb_engine* e) {
+// Status record of the latest sphb_mg_unpack_async, once the GPU has produced it.  wait = block on its event (recorded
+// before the kernels of the following step, so by the time the next pack asks it has long completed and nothing drains).
+int poll_status(sphb_engine* e, bool wait) {
+    if (e->status_seen == e->status_issued) return SPHB_OK;
+    const int slot = (int)((e->status_issued - 1) & 1);
+    if (wait) CK(cudaEventSynchronize(e->ev_status[slot]));
+    else {
+        cudaError_t q = cudaEventQuery(e->ev_status[slot]);
+        if (q == cudaErrorNotReady) return SPHB_OK;
+        CK(q);
+    }
+    memcpy(e->last_status, e->h_status + 8 * slot, sizeof e->last_status);
+    e->status_seen = e->status_issued;
+    const int* h = e->last_status;
+    e->mg_sent[0] = (size_t)h[5];
+    e->mg_sent[1] = (size_t)h[6];
+    if (e->n_deferred && e->cnt_slot == 0) e->n = (size_t)h[3]; // still before the sort: this IS the count
+    if (h[7] & 3) {
+        e->have_state = false;
+        return fail(SPHB_ERR_CAPACITY, "a neighbour overflowed its message in the last exchange (flags %d): particles were lost, the state is dropped", h[7]);
+    }
+    if (h[7] & 4) {
+        e->have_state = false;
+        return fail(SPHB_ERR_CAPACITY, "the particle arrays overflowed in the last exchange: call sphb_reserve with more room (the state is dropped)");
+    }
+    return SPHB_OK;
+}
+
+// Make e->n exact again after sphb_mg_unpack_async left it as an estimate (synchronises).
+int resolve_counts(sphb_engine* e) {
+    if (!e->n_deferred) return SPHB_OK;
+    int h[2] = {0, 0};
+    CK(cudaMemcpyAsync(h, e->d_cnt, sizeof h, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    int rc = poll_status(e, true);
+    e->n = (size_t)h[e->cnt_slot];
+    e->n_dead = e->cnt_slot == 0 ? (size_t)e->last_status[4] : 0; // before the sort the dead are still among the n
+    e->n_deferred = false;
+    return rc;
+}
+
+int check_ready_hot(sphb_engine* e) { // the entry points of the per-step loop: never wait for the GPU
     if (!e) return fail(SPHB_ERR_INVALID, "null engine");
     if (!e->have_state) return fail(SPHB_ERR_STATE, "no particles uploaded");
     return use_device(e);
+}
+
+int check_ready(sphb_engine* e) {
+    int rc = check_ready_hot(e);
+    if (rc) return rc;
+    return resolve_counts(e);
 }
 
 } // namespace
@@ -376,6 +466,9 @@ int sphb_create(const sphb_params* p, int device, sphb_engine** out) {
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_grid, sizeof(GridDesc));
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_bbox, sizeof(BBoxAcc));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_cnt, 8 * sizeof(int));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_status, 8 * sizeof(int));
+    if (err == cudaSuccess) err = cudaMemsetAsync(e->d_cnt, 0, 8 * sizeof(int), e->stream);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->d_stats, 4 * sizeof(unsigned int));
     if (err == cudaSuccess) err = cudaMemsetAsync(e->d_stats, 0, 4 * sizeof(unsigned int), e->stream);
     if (err != cudaSuccess) {
@@ -395,11 +488,16 @@ void sphb_destroy(sphb_engine* e) {
         e->posm[b].release(); e->vel[b].release(); e->aux[b].release(); e->accel[b].release(); e->oid[b].release();
     }
     e->key.release(); e->slot.release(); e->inv.release(); e->pairs.release(); e->mask.release(); e->vr.release();
-    e->cell_start.release(); e->block_sums.release(); e->row_groups.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release(); e->contacts.release();
+    e->cell_start.release(); e->block_sums.release(); e->row_groups.release(); e->aos.release(); e->scratch.release(); e->mg_counts.release(); e->contacts.release(); e->warp_box.release();
     if (e->d_spheres) cudaFree(e->d_spheres);
     if (e->d_grid) cudaFree(e->d_grid);
     if (e->d_bbox) cudaFree(e->d_bbox);
     if (e->d_stats) cudaFree(e->d_stats);
+    if (e->d_cnt) cudaFree(e->d_cnt);
+    if (e->d_status) cudaFree(e->d_status);
+    if (e->h_status) cudaFreeHost(e->h_status);
+    for (int k = 0; k < 2; k++)
+        if (e->ev_status[k]) cudaEventDestroy(e->ev_status[k]);
     if (e->ev) {
         for (int i = 0; i < 4 * sphb_engine::kMaxTimed; i++) cudaEventDestroy(e->ev[i]);
         delete[] e->ev;
@@ -480,11 +578,14 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
     }
     e->have_state = true;
     e->n_dead = 0;
+    e->n_deferred = false;
+    e->status_seen = e->status_issued;
     e->oid_identity = false;
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->box_records = 0;
     e->mg_pending = false;
     e->aos_valid = true;
     return SPHB_OK;
@@ -529,11 +630,14 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
     }
     e->have_state = true;
     e->n_dead = 0;
+    e->n_deferred = false;
+    e->status_seen = e->status_issued;
     e->oid_identity = false;
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->box_records = 0;
     e->mg_pending = false;
     e->aos_valid = false;
     return SPHB_OK;
@@ -676,10 +780,10 @@ int sphb_update_forces(sphb_engine* e) {
     // vr_valid: rho/P in aux are this engine's own (update_density ran on this sorted state) -> two-gather kernel
     auto kfn = e->vr_valid ? force_kernel<false, false, true, true>(e->rows) : force_kernel<false, false, true, false>(e->rows);
     LAUNCH(e, kfn, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p,
-           e->aux[cur].p, e->vr.p, e->mask.p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, e->d_bbox, n);
+           e->aux[cur].p, e->vr.p, e->mask.p, e->accel[cur].p, (float4*)nullptr, (float4*)nullptr, (float4*)nullptr, n, (const int*)nullptr, (int)e->mstride, 0);
     if (e->params.laplacian_viscosity)
         LAUNCH(e, k_lap_viscosity, cdiv(n, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p,
-               e->mask.p, e->accel[cur].p, n);
+               e->mask.p, e->accel[cur].p, n, (int)e->mstride);
     CK(cudaGetLastError());
     return SPHB_OK;
 }
@@ -696,6 +800,7 @@ int sphb_update_posvel(sphb_engine* e) {
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->box_records = 0;
     return SPHB_OK;
 }
 
@@ -711,15 +816,23 @@ int sphb_collision(sphb_engine* e) {
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->box_records = 0;
     return SPHB_OK;
 }
 
 int sphb_step(sphb_engine* e, int nsteps) {
-    int rc = check_ready(e);
+    int rc = check_ready_hot(e);
+    if (!rc && e->n_deferred && (e->nspheres || e->params.laplacian_viscosity || e->rows != 9)) rc = resolve_counts(e); // those paths size work from the host's n
     if (rc) return rc;
     if (nsteps < 0) return fail(SPHB_ERR_INVALID, "nsteps < 0");
     if (e->n == 0) return SPHB_OK;
-    const bool bbox = !e->c.domain_fixed;
+    // Bounding-box grid mode: the box of the new positions comes from one streaming pass at the start of the next sort (k_bbox,
+    // 16 B/particle: 0.05 ms at 16.7 M).  Tracking it inside the fused force kernel instead (SPHB_BBOX_FUSED=1: per-warp boxes,
+    // joined by k_bbox_fold) costs that kernel six live registers and 0.17 ms; earlier forms of the fold cost 0.36 - 0.5 ms.
+#ifndef SPHB_BBOX_FUSED
+#define SPHB_BBOX_FUSED 0
+#endif
+    const bool bbox = SPHB_BBOX_FUSED && !e->c.domain_fixed;
     const bool acc = e->params.write_accel != 0;
     if (e->params.laplacian_viscosity) { // optional extra force pass: run the phases one by one
         for (int s = 0; s < nsteps; s++)
@@ -740,13 +853,21 @@ int sphb_step(sphb_engine* e, int nsteps) {
         if (timed) CK(cudaEventRecord(ev[2], e->stream));
         const int cur = e->cur, nxt = cur ^ 1;
         const int blocks = cdiv(n, 128);
-#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->vr.p, e->mask.p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->d_bbox, n
+#define FORCE_ARGS e->c, e->d_grid, e->cell_start.p, e->posm[cur].p, e->vel[cur].p, e->aux[cur].p, e->vr.p, e->mask.p, e->accel[nxt].p, e->posm[nxt].p, e->vel[nxt].p, e->warp_box.p, n, n_dev(e), (int)e->mstride
         auto kfn = bbox ? (acc ? force_kernel<true, true, true, true>(e->rows) : force_kernel<true, true, false, true>(e->rows))
                         : (acc ? force_kernel<true, false, true, true>(e->rows) : force_kernel<true, false, false, true>(e->rows));
-        if (n <= kSmallScene && e->rows == 9) // small scene: four neighbours in flight per thread (latency, not throughput)
+        if (n <= kSmallScene && e->rows == 9 && !e->n_deferred) // small scene: four neighbours in flight per thread (latency, not throughput)
             kfn = bbox ? (acc ? k_force<true, true, true, 9, true, 4> : k_force<true, true, false, 9, true, 4>)
                        : (acc ? k_force<true, false, true, 9, true, 4> : k_force<true, false, false, 9, true, 4>);
-        LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS);
+        LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS, 0);
+        int box_records = bbox ? blocks * 4 : 0;
+        if (e->n_deferred) { // n was an estimate: a few blocks walk whatever particles lie beyond the main launch (normally none)
+            constexpr int kTail = 148;
+            auto ktail = bbox ? (acc ? k_force<true, true, true, 9, true, 1, true> : k_force<true, true, false, 9, true, 1, true>)
+                              : (acc ? k_force<true, false, true, 9, true, 1, true> : k_force<true, false, false, 9, true, 1, true>);
+            LAUNCH(e, ktail, kTail, 128, 0, FORCE_ARGS, blocks * 128);
+            if (bbox) box_records += kTail * 4;
+        }
 #undef FORCE_ARGS
         CK(cudaGetLastError());
         // the new state (posm, vel, accel) is in nxt; aux (rho, P) and ids stay where they are: copy-free
@@ -759,7 +880,8 @@ int sphb_step(sphb_engine* e, int nsteps) {
         e->grid_valid = false;
         e->mask_valid = false;
         e->vr_valid = false;
-        e->bbox_valid = bbox;
+        e->bbox_valid = false;
+        e->box_records = box_records; // joined into the box at the start of the next sort (ensure_bbox)
         if (e->nspheres) { // the same order as step_scene: forces, posvel (spheres after particles), collision
             LAUNCH(e, k_sphere_forces, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
             LAUNCH(e, k_sphere_posvel, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
@@ -852,7 +974,7 @@ int sphb_get_bbox(sphb_engine* e, float bbox[6]) {
     if (rc) return rc;
     if (!bbox) return fail(SPHB_ERR_INVALID, "null bbox");
     if (e->n == 0) return fail(SPHB_ERR_STATE, "no particles");
-    if (!e->bbox_valid && (rc = run_bbox(e))) return rc;
+    if ((rc = ensure_bbox(e))) return rc;
     BBoxAcc acc;
     CK(cudaMemcpyAsync(&acc, e->d_bbox, sizeof acc, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
@@ -866,7 +988,12 @@ int sphb_get_bbox(sphb_engine* e, float bbox[6]) {
     return SPHB_OK;
 }
 
-size_t sphb_count(const sphb_engine* e) { return e ? e->n : 0; }
+size_t sphb_count(const sphb_engine* e) {
+    if (!e) return 0;
+    sphb_engine* m = const_cast<sphb_engine*>(e);
+    if (m->n_deferred && cudaSetDevice(m->device) == cudaSuccess) resolve_counts(m); // after sphb_mg_unpack_async: fetch the count (synchronises)
+    return e->n;
+}
 
 int sphb_count_nonfinite(sphb_engine* e, size_t* count) {
     int rc = check_ready(e);
@@ -993,8 +1120,9 @@ extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_lef
 }
 
 extern "C" int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* msg_left, size_t cap_left, void* msg_right, size_t cap_right) {
-    int rc = check_ready(e);
+    int rc = check_ready_hot(e);
     if (rc) return rc;
+    if ((rc = poll_status(e, true))) return rc; // the last asynchronous unpack's verdict (overflow) and counts: long since on the host
     if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
     if ((slab->has_left && !msg_left) || (slab->has_right && !msg_right)) return fail(SPHB_ERR_INVALID, "missing message buffer");
     if (cap_left > 0x3fffffffu || cap_right > 0x3fffffffu) return fail(SPHB_ERR_CAPACITY, "message capacity too large");
@@ -1006,16 +1134,18 @@ extern "C" int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* 
     s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
     s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
     s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
-    const int n = (int)e->n, cur = e->cur;
-    const int nb = n ? cdiv(n, kMgTile) : 1;
-    CK(e->mg_counts.reserve((size_t)kMgStreams * nb + 16 + 2 * (size_t)nb)); // counts, totals + received counts, one byte per warp
-    e->mg_blocks = nb;
-    int* totals = e->mg_counts.p + kMgStreams * nb;
-    unsigned char* touch = (unsigned char*)(totals + 16);
-    LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, touch);
-    LAUNCH(e, k_mg_scan, kMgStreams, kMgScanThreads, 0, e->mg_counts.p, nb, n, totals);
+    const int n = (int)e->n, cur = e->cur; // n: an estimate while the count lives on the device (the kernels read the real one)
     const int out_cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
-    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, e->mg_counts.p, totals, out_cap, touch,
+    const int nb_layout = cdiv(out_cap > 0 ? out_cap : 1, kMgTile); // arrays laid out for the capacity: the count may not be known here
+    const int nb = n ? cdiv(n, kMgTile) : 1;
+    CK(e->mg_counts.reserve((size_t)kMgStreams * nb_layout + 16 + 2 * (size_t)nb_layout)); // counts, totals + received counts, one byte per warp
+    e->mg_blocks = nb_layout;
+    int* totals = e->mg_counts.p + kMgStreams * nb_layout;
+    unsigned char* touch = (unsigned char*)(totals + 16);
+    const int* nd = n_dev(e);
+    LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, nd, nb_layout, e->mg_counts.p, touch);
+    LAUNCH(e, k_mg_scan, kMgStreams, kMgScanThreads, 0, e->mg_counts.p, nb_layout, n, nd, totals);
+    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, nd, nb_layout, e->mg_counts.p, totals, out_cap, touch,
            (float4*)msg_left, (float4*)msg_right, (int)cap_left, (int)cap_right);
     CK(cudaGetLastError());
     e->mg_pending = true;
@@ -1029,8 +1159,72 @@ extern "C" int sphb_mg_sent(sphb_engine* e, size_t sent[2]) {
     return SPHB_OK;
 }
 
+namespace {
+Slab to_slab(const sphb_slab* slab) {
+    Slab s;
+    s.lo = slab->lo; s.hi = slab->hi; s.halo = slab->halo;
+    s.has_left = slab->has_left; s.has_right = slab->has_right;
+    s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
+    s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
+    s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
+    return s;
+}
+} // namespace
+
+extern "C" int sphb_mg_unpack_async(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right) {
+    int rc = check_ready_hot(e);
+    if (rc) return rc;
+    if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
+    if (!e->mg_pending) return fail(SPHB_ERR_STATE, "sphb_mg_unpack_async without sphb_mg_pack");
+    if (!e->h_status) {
+        CK(cudaMallocHost((void**)&e->h_status, 16 * sizeof(int)));
+        memset(e->h_status, 0, 16 * sizeof(int));
+        for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&e->ev_status[k], cudaEventDisableTiming));
+    }
+    const Slab s = to_slab(slab);
+    const int cur = e->cur;
+    int* totals = e->mg_counts.p + kMgStreams * e->mg_blocks;
+    int* recv = totals + 4;
+    const int cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
+    CK(cudaMemsetAsync(recv, 0, 4 * sizeof(int), e->stream));
+    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, cap, recv);
+    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, cap, recv);
+    LAUNCH(e, k_mg_commit, 1, 32, 0, totals, recv, cap, e->d_cnt, e->d_status);
+    CK(cudaGetLastError());
+    const int slot = (int)(e->status_issued & 1);
+    CK(cudaMemcpyAsync(e->h_status + 8 * slot, e->d_status, 8 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaEventRecord(e->ev_status[slot], e->stream));
+    e->status_issued++;
+    e->mg_pending = false;
+    // the host's estimate of the new count (launch sizing only): last exchange's total plus 3 % + 8192, or everything the arrays hold
+    const size_t last = (size_t)e->last_status[3];
+    size_t est = last ? last + last / 32 + 8192 : (size_t)cap;
+    if (est > (size_t)cap) est = (size_t)cap;
+    e->n = est;
+    e->n_deferred = true;
+    e->cnt_slot = 0;
+    e->oid_identity = true; // ids restart at the slot numbers; the next sort reads them as such without an array
+    e->grid_valid = false;
+    e->mask_valid = false;
+    e->vr_valid = false;
+    e->bbox_valid = false;
+    e->box_records = 0;
+    e->aos_valid = false;
+    return SPHB_OK;
+}
+
+extern "C" int sphb_mg_poll(sphb_engine* e, size_t status[8], int wait) {
+    if (!e || !status) return fail(SPHB_ERR_INVALID, "null argument");
+    int rc = use_device(e);
+    if (rc) return rc;
+    rc = poll_status(e, wait != 0);
+    for (int k = 0; k < 8; k++) status[k] = (size_t)e->last_status[k];
+    status[7] = (size_t)e->status_seen;
+    return rc;
+}
+
 extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, size_t counts[4]) {
-    int rc = check_ready(e);
+    int rc = check_ready_hot(e);
     if (rc) return rc;
     if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
     if (!e->mg_pending) return fail(SPHB_ERR_STATE, "sphb_mg_unpack without sphb_mg_pack");
@@ -1057,14 +1251,25 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     e->n_dead = (size_t)h[3]; // marked in place by the pack, whatever happens below
     e->mg_sent[0] = (size_t)h[1];
     e->mg_sent[1] = (size_t)h[2];
-    if (h[6] > cl || h[7] > cr) return fail(SPHB_ERR_CAPACITY, "a neighbour overflowed its message (wanted %d / %d records)", h[6], h[7]);
-    if (total > cap) return fail(SPHB_ERR_CAPACITY, "%lld particles exceed the reserved %d: call sphb_reserve with more room", total, cap);
+    // An overflow cannot be repaired here: the senders have already handed ownership over and marked their copies dead, so the
+    // records that did not fit are gone.  The engine refuses to go on with a half-updated state (upload again, with more room).
+    if (h[6] > cl || h[7] > cr) {
+        e->have_state = false;
+        return fail(SPHB_ERR_CAPACITY, "a neighbour overflowed its message (wanted %d / %d records): particles were lost, the state is dropped", h[6], h[7]);
+    }
+    if (total > cap) {
+        e->have_state = false;
+        return fail(SPHB_ERR_CAPACITY, "%lld particles exceed the reserved %d: call sphb_reserve with more room (the state is dropped)", total, cap);
+    }
     e->n = (size_t)total;
+    e->n_deferred = false; // the count is exact again
+    e->last_status[3] = (int)total;
     e->oid_identity = true; // ids restart at the slot numbers; the next sort reads them as such without an array
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
     e->bbox_valid = false;
+    e->box_records = 0;
     e->aos_valid = false;
     if (counts) { counts[0] = (size_t)kept; counts[1] = (size_t)cl; counts[2] = (size_t)cr; counts[3] = (size_t)total; }
     return SPHB_OK;

@@ -74,6 +74,11 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
     }
 }
 
+// Resident blocks per SM the main force kernel is compiled for: 9 blocks of 128 threads = 56 registers (measured against 8 blocks /
+// 64 registers); the latency-oriented small-scene variant (kIlp = 4) and the 25-row variant take what they need.
+#ifndef SPHB_FORCE_MINBLOCKS
+#define SPHB_FORCE_MINBLOCKS 9
+#endif
 #ifndef SPHB_FORCE_WORDS
 #define SPHB_FORCE_WORDS 13
 #endif
@@ -92,12 +97,12 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
 // kIlp:   neighbours fetched per iteration.  1 for real workloads (more only cost registers there); 4 for small scenes,
 //         where a handful of warps per SM hide nothing and a thread's chain of L2-latency gathers IS the kernel time:
 //         four neighbours' records are requested before the first is used.  Same accumulation order, same bits.
-template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp = 1>
-__global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
-                                               const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
-                                               const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
-                                               float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
-                                               BBoxAcc* bbox, int n) {
+template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp>
+__device__ __forceinline__ void force_thread(const Consts& c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                             const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
+                                             const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
+                                             float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                             const int n, const int ms /* stride of the mask rows */, const int i, float lo[3], float hi[3]) {
     // kRows == 9: this thread's NON-EMPTY mask words, compacted, each with the sorted slot of its bit 0 -- one LDS.64 per
     // refill.  kRows == 25 would need 51 KB that way (static shared memory ends at 48 KB): there the words are kept with
     // their index (2*row + half) and the rows' run starts separately.
@@ -113,8 +118,6 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
     __shared__ unsigned char s_idx[kPairs ? 1 : 2 * kRows][128];
     __shared__ int s_jb[kPairs ? 1 : kRows][128];
     const int tid = threadIdx.x;
-    const int i = blockIdx.x * blockDim.x + tid;
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     if (i < n) {
         const GridDesc g = *gd;
         const float4 pi = ldg4(posm + i);
@@ -131,7 +134,7 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             unsigned int mw[18];
             int jbr[9], jer[9];
 #pragma unroll
-            for (int w = 0; w < 18; w++) mw[w] = __ldg(mask + (size_t)w * n + i);
+            for (int w = 0; w < 18; w++) mw[w] = __ldg(mask + (size_t)w * ms + i);
             const int x0 = max(cx - g.stencil_x, 0), x1 = min(cx + g.stencil_x, g.dims[0] - 1) + 1;
 #pragma unroll
             for (int r = 0; r < 9; r++) {
@@ -161,7 +164,7 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             for (int r = 0; r < kRows; r++) {
                 int jb, je;
                 row_run(g, cell_start, cx, cy, cz, r, jb, je);
-                const unsigned int m0 = mask[(size_t)(2 * r) * n + i], m1 = mask[(size_t)(2 * r + 1) * n + i];
+                const unsigned int m0 = mask[(size_t)(2 * r) * ms + i], m1 = mask[(size_t)(2 * r + 1) * ms + i];
                 s_jb[r][tid] = jb;
                 if (m0) { s_word[nw][tid] = m0; s_idx[nw][tid] = (unsigned char)(2 * r); nw++; }
                 if (m1) { s_word[nw][tid] = m1; s_idx[nw][tid] = (unsigned char)(2 * r + 1); nw++; }
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
         }
         if (kPairs && nw > kCapW) { // the words that did not fit the staging area, in the same order
             for (int ww = first_over; ww < 2 * kRows; ww++) {
-                unsigned int mo = __ldg(mask + (size_t)ww * n + i);
+                unsigned int mo = __ldg(mask + (size_t)ww * ms + i);
                 if (!mo) continue;
                 int jb2, je2;
                 row_run(g, cell_start, cx, cy, cz, ww >> 1, jb2, je2);
@@ -272,15 +275,64 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
             collide_walls(c, p, v);
             posm_out[i] = p;
             vel_out[i] = v;
-            if (kBBox) {
-                lo[0] = hi[0] = p.x; lo[1] = hi[1] = p.y; lo[2] = hi[2] = p.z;
-#pragma unroll
-                for (int a = 0; a < 3; a++)
-                    if (!(lo[a] == lo[a])) { lo[a] = INFINITY; hi[a] = -INFINITY; } // NaN: ignored like the reference's compares
+            if (kBBox) { // fminf/fmaxf drop NaNs, like the reference's `if (x < min)` comparisons
+                lo[0] = fminf(lo[0], p.x); hi[0] = fmaxf(hi[0], p.x);
+                lo[1] = fminf(lo[1], p.y); hi[1] = fmaxf(hi[1], p.y);
+                lo[2] = fminf(lo[2], p.z); hi[2] = fmaxf(hi[2], p.z);
             }
         }
     }
-    if (kFused && kBBox) bbox_block_commit(lo, hi, bbox);
+}
+
+// The kernel: thread i takes sorted particle first + i.  n_dev (may be null) = the live count on the device when the host
+// only has an estimate of it (sphb_mg_unpack_async): the main launch (kLoop = false) covers the estimate, and a small second
+// launch with kLoop = true, first = threads of the main launch, walks whatever lies beyond in grid strides -- normally
+// nothing.  ms = stride of the mask rows (a capacity).  kBBox: every warp leaves the box of its new positions in
+// warp_box[global warp id] (8 floats: min xyz, -, max xyz, -); k_bbox_fold joins them at the start of the next sort.  (Folding
+// into ONE global box from here -- per block behind a barrier, or per warp -- cost 0.36 / 0.5 ms at 16.7 M: the barrier keeps
+// blocks resident for their slowest warp, and half a million warps polling one L2 line queue up behind each other.)
+template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp = 1, bool kLoop = false>
+__global__ void __launch_bounds__(128, (kRows == 9 && kIlp == 1) ? SPHB_FORCE_MINBLOCKS : 1) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
+                                               const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
+                                               const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
+                                               float4* __restrict__ accel, float4* __restrict__ posm_out, float4* __restrict__ vel_out,
+                                               float4* __restrict__ warp_box, int n, const int* __restrict__ n_dev, int ms, int first) {
+    if (n_dev) n = *n_dev;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (!kLoop) {
+        force_thread<kFused, kBBox, kAccel, kRows, kDerive, kIlp>(c, gd, cell_start, posm, vel, aux, vr, mask, accel, posm_out, vel_out, n, ms,
+                                                                  first + blockIdx.x * blockDim.x + threadIdx.x, lo, hi);
+    } else {
+        for (long long base = first + (long long)blockIdx.x * blockDim.x; base < n; base += (long long)gridDim.x * blockDim.x)
+            force_thread<kFused, kBBox, kAccel, kRows, kDerive, kIlp>(c, gd, cell_start, posm, vel, aux, vr, mask, accel, posm_out, vel_out, n, ms,
+                                                                      (int)base + (int)threadIdx.x, lo, hi);
+    }
+    if (kFused && kBBox) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+                hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+            }
+        }
+        if ((threadIdx.x & 31) == 0) {
+            float4* w = warp_box + 2 * (size_t)((first / 32) + blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5));
+            w[0] = make_float4(lo[0], lo[1], lo[2], 0.0f);
+            w[1] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+        }
+    }
+}
+
+// Joins the per-warp boxes the fused force kernel left (count records of 8 floats) into the global accumulator.
+__global__ void __launch_bounds__(256) k_bbox_fold(const float4* __restrict__ warp_box, int count, BBoxAcc* acc) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const float4 l = warp_box[2 * (size_t)i], h = warp_box[2 * (size_t)i + 1];
+        lo[0] = fminf(lo[0], l.x); lo[1] = fminf(lo[1], l.y); lo[2] = fminf(lo[2], l.z);
+        hi[0] = fmaxf(hi[0], h.x); hi[1] = fmaxf(hi[1], h.y); hi[2] = fmaxf(hi[2], h.z);
+    }
+    bbox_block_commit(lo, hi, acc);
 }
 
 // Optional: the reference's dead viscosity_forces (SphUtils.cpp:244-290; its call at :175 is commented out), on
@@ -288,7 +340,7 @@ __global__ void __launch_bounds__(128) k_force(Consts c, const GridDesc* __restr
 // (:84-95).  A separate pass over the neighbour masks that adds into accel; row by row, off the hot path.
 __global__ void __launch_bounds__(128) k_lap_viscosity(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                        const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
-                                                       const unsigned int* __restrict__ mask, float4* __restrict__ accel, int n) {
+                                                       const unsigned int* __restrict__ mask, float4* __restrict__ accel, int n, int ms) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const GridDesc g = *gd;
@@ -311,7 +363,7 @@ __global__ void __launch_bounds__(128) k_lap_viscosity(Consts c, const GridDesc*
         int jb, je;
         row_run(g, cell_start, cx, cy, cz, r, jb, je);
         for (int w = 0; w < 2; w++) {
-            unsigned int m = mask[(size_t)(2 * r + w) * n + i];
+            unsigned int m = mask[(size_t)(2 * r + w) * ms + i];
             while (m) {
                 pair(jb + 32 * w + __ffs((int)m) - 1);
                 m &= m - 1;

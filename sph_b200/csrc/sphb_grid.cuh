@@ -125,22 +125,23 @@ __device__ __forceinline__ int cell_key(const GridDesc& g, float x, float y, flo
     return cx + g.dims[0] * (cy + g.dims[1] * cz);
 }
 
-__global__ void __launch_bounds__(256) k_key_hist(const GridDesc* __restrict__ gd, const float4* __restrict__ posm, int n,
+__global__ void __launch_bounds__(256) k_key_hist(const GridDesc* __restrict__ gd, const float4* __restrict__ posm, int n, const int* __restrict__ n_dev,
                                                   int* __restrict__ key, int* __restrict__ slot, int* __restrict__ cell_count,
                                                   BBoxAcc* acc, int rearm_bbox, int trash) {
     const GridDesc g = *gd;
+    if (n_dev) n = *n_dev; // the count lives on the device (sphb_mg_unpack_async); the launch was sized from an estimate
     if (rearm_bbox && blockIdx.x == 0 && threadIdx.x < 3) {
         acc->lo[threadIdx.x] = f2ord(INFINITY);
         acc->hi[threadIdx.x] = f2ord(-INFINITY);
     }
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float4 p = ldg4(posm + i);
-    int cx, cy, cz;
-    int k = cell_key(g, p.x, p.y, p.z, cx, cy, cz);
-    if (trash && p.w < 0.0f) k = g.ncell + (i & (kTrashBins - 1)); // marked dead by sphb_mg_pack: filed behind the last cell
-    key[i] = k;
-    slot[i] = atomicAdd(cell_count + k, 1);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float4 p = ldg4(posm + i);
+        int cx, cy, cz;
+        int k = cell_key(g, p.x, p.y, p.z, cx, cy, cz);
+        if (trash && p.w < 0.0f) k = g.ncell + (i & (kTrashBins - 1)); // marked dead by sphb_mg_pack: filed behind the last cell
+        key[i] = k;
+        slot[i] = atomicAdd(cell_count + k, 1);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------

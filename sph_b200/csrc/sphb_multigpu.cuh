@@ -120,42 +120,50 @@ __device__ __forceinline__ unsigned long long mg_block_scan(unsigned long long v
     return off + inc - v;
 }
 
-// pass 1: per-block record counts, one array per stream: block_counts[k * nblocks + block]
+// pass 1: per-tile record counts, one array per stream: block_counts[k * nb_layout + tile].  n_dev (may be null) = the particle
+// count on the device when the host only has an estimate (sphb_mg_unpack_async): blocks then walk the tiles in grid strides;
+// nb_layout = tiles the arrays were laid out for (from the capacity).
 __global__ void __launch_bounds__(kMgThreads) k_mg_count(Slab s, const float4* __restrict__ posm, const float4* __restrict__ vel, int n,
+                                                         const int* __restrict__ n_dev, int nb_layout,
                                                          int* __restrict__ block_counts, unsigned char* __restrict__ touch) {
-    const int i0 = blockIdx.x * kMgTile + threadIdx.x * kMgPer;
-    unsigned long long c = 0;
-    bool work = false; // something for pass 3 to do here: records to emit, a flag / wrap to write back, a particle to mark dead
-    float4 p[kMgPer], v[kMgPer];
-#pragma unroll
-    for (int q = 0; q < kMgPer; q++) {
-        const int i = max(min(i0 + q, n - 1), 0);
-        p[q] = ldg4(posm + i);
-        v[q] = ldg4(vel + i);
-    }
-#pragma unroll
-    for (int q = 0; q < kMgPer; q++) {
-        if (i0 + q >= n) break;
-        const MgItem it = mg_classify(s, p[q], v[q]);
-        c += mg_pack4(it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0, it.dead ? 1 : 0);
-        work |= it.left || it.right || it.dies ||
-                (it.keep && (it.nimg > 1 || it.p.y != p[q].y || it.p.z != p[q].z || (mg_inside(s, it.p) ? 1.0f : 0.0f) != v[q].w));
-    }
-    // one byte per warp (128 consecutive particles): pass 3 skips the warps with nothing to do -- away from the slab
-    // faces that is most of them -- without reading their particles again
-    const bool any = __any_sync(0xffffffffu, work);
-    if ((threadIdx.x & 31) == 0) touch[blockIdx.x * (kMgThreads / 32) + (threadIdx.x >> 5)] = any ? 1 : 0;
-    // block sum only: warp reduction, then one shared-memory round
+    if (n_dev) n = *n_dev;
+    const int ntiles = (n + kMgTile - 1) / kMgTile;
     __shared__ unsigned long long s_part[kMgThreads / 32];
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int i0 = tile * kMgTile + threadIdx.x * kMgPer;
+        unsigned long long c = 0;
+        bool work = false; // something for pass 3 to do here: records to emit, a flag / wrap to write back, a particle to mark dead
+        float4 p[kMgPer], v[kMgPer];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = c;
-    __syncthreads();
-    if (threadIdx.x < kMgStreams) {
-        unsigned long long tot = 0;
+        for (int q = 0; q < kMgPer; q++) {
+            const int i = max(min(i0 + q, n - 1), 0);
+            p[q] = ldg4(posm + i);
+            v[q] = ldg4(vel + i);
+        }
 #pragma unroll
-        for (int w = 0; w < kMgThreads / 32; w++) tot += s_part[w];
-        block_counts[threadIdx.x * gridDim.x + blockIdx.x] = mg_field(tot, threadIdx.x);
+        for (int q = 0; q < kMgPer; q++) {
+            if (i0 + q >= n) break;
+            const MgItem it = mg_classify(s, p[q], v[q]);
+            c += mg_pack4(it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0, it.dead ? 1 : 0);
+            work |= it.left || it.right || it.dies ||
+                    (it.keep && (it.nimg > 1 || it.p.y != p[q].y || it.p.z != p[q].z || (mg_inside(s, it.p) ? 1.0f : 0.0f) != v[q].w));
+        }
+        // one byte per warp (128 consecutive particles): pass 3 skips the warps with nothing to do -- away from the slab
+        // faces that is most of them -- without reading their particles again
+        const bool any = __any_sync(0xffffffffu, work);
+        if ((threadIdx.x & 31) == 0) touch[tile * (kMgThreads / 32) + (threadIdx.x >> 5)] = any ? 1 : 0;
+        // block sum only: warp reduction, then one shared-memory round
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = c;
+        __syncthreads();
+        if (threadIdx.x < kMgStreams) {
+            unsigned long long tot = 0;
+#pragma unroll
+            for (int w = 0; w < kMgThreads / 32; w++) tot += s_part[w];
+            block_counts[threadIdx.x * nb_layout + tile] = mg_field(tot, threadIdx.x);
+        }
+        __syncthreads(); // s_part is reused by the next tile
     }
 }
 
@@ -164,8 +172,11 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_count(Slab s, const float4* _
 // 256-thread block for all three streams, took 0.34 ms of a 7.4 ms step at 17.8 M particles).
 constexpr int kMgScanThreads = 1024;
 
-__global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ block_counts, int nblocks, int n, int* __restrict__ totals) {
+__global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ block_counts, int nb_layout, int n, const int* __restrict__ n_dev,
+                                                           int* __restrict__ totals) {
     __shared__ int s_warp[kMgScanThreads / 32];
+    if (n_dev) n = *n_dev;
+    const int nblocks = (n + kMgTile - 1) / kMgTile;
     const int k = blockIdx.x; // stream
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int carry = 0;
@@ -175,7 +186,7 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
         int tsum = 0;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            v[q] = (b0 + q < nblocks) ? block_counts[k * nblocks + b0 + q] : 0;
+            v[q] = (b0 + q < nblocks) ? block_counts[k * nb_layout + b0 + q] : 0;
             tsum += v[q];
         }
         int inc = tsum;
@@ -200,7 +211,7 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
         const int round_total = s_warp[kMgScanThreads / 32 - 1];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            if (b0 + q < nblocks) block_counts[k * nblocks + b0 + q] = ex;
+            if (b0 + q < nblocks) block_counts[k * nb_layout + b0 + q] = ex;
             ex += v[q];
         }
         carry += round_total;
@@ -214,72 +225,77 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
 // pass 3: write.  A kept particle stays in its slot (flag refreshed, wrapped coordinates written back); its periodic
 // images go behind the current particles (slot n + offset); a dropped one is marked dead; left/right -> messages.
 // posm/vel are read and written by the thread that owns slot i only.
-__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restrict__ posm, float4* __restrict__ vel, int n,
-                                                         const int* __restrict__ block_offsets, const int* __restrict__ totals,
+__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restrict__ posm, float4* __restrict__ vel, int n, const int* __restrict__ n_dev,
+                                                         int nb_layout, const int* __restrict__ block_offsets, const int* __restrict__ totals,
                                                          int out_capacity, const unsigned char* __restrict__ touch,
                                                          float4* __restrict__ msg_left, float4* __restrict__ msg_right, int cap_left, int cap_right) {
-    const int i0 = blockIdx.x * kMgTile + threadIdx.x * kMgPer;
-    const bool active = touch[blockIdx.x * (kMgThreads / 32) + (threadIdx.x >> 5)] != 0; // warp-uniform
-    // phase 1: this thread's record counts (nothing is kept in registers: phase 2 reads the four particles again,
-    // from L1 -- holding them cost 107 registers and three quarters of the occupancy)
-    unsigned long long mine = 0;
-    if (active) {
-        float4 pp[kMgPer], vv[kMgPer];
+    if (n_dev) n = *n_dev;
+    const int ntiles = (n + kMgTile - 1) / kMgTile;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int i0 = tile * kMgTile + threadIdx.x * kMgPer;
+        const bool active = touch[tile * (kMgThreads / 32) + (threadIdx.x >> 5)] != 0; // warp-uniform
+        // phase 1: this thread's record counts (nothing is kept in registers: phase 2 reads the four particles again,
+        // from L1 -- holding them cost 107 registers and three quarters of the occupancy)
+        unsigned long long mine = 0;
+        if (active) {
+            float4 pp[kMgPer], vv[kMgPer];
 #pragma unroll
-        for (int q = 0; q < kMgPer; q++) {
-            const int i = max(min(i0 + q, n - 1), 0);
-            pp[q] = posm[i];
-            vv[q] = vel[i];
+            for (int q = 0; q < kMgPer; q++) {
+                const int i = max(min(i0 + q, n - 1), 0);
+                pp[q] = posm[i];
+                vv[q] = vel[i];
+            }
+#pragma unroll
+            for (int q = 0; q < kMgPer; q++) {
+                if (i0 + q >= n) break;
+                const MgItem it = mg_classify(s, pp[q], vv[q]);
+                mine += mg_pack4(it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0, 0);
+            }
         }
+        unsigned long long tot;
+        const unsigned long long ex = mg_block_scan(mine, &tot);
+        int off[3];
 #pragma unroll
-        for (int q = 0; q < kMgPer; q++) {
-            if (i0 + q >= n) break;
-            const MgItem it = mg_classify(s, pp[q], vv[q]);
-            mine += mg_pack4(it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0, 0);
-        }
-    }
-    unsigned long long tot;
-    const unsigned long long ex = mg_block_scan(mine, &tot);
-    int off[3];
-#pragma unroll
-    for (int k = 0; k < 3; k++) off[k] = mg_field(ex, k) + block_offsets[k * gridDim.x + blockIdx.x];
+        for (int k = 0; k < 3; k++) off[k] = mg_field(ex, k) + block_offsets[k * nb_layout + tile];
 #pragma unroll 1
-    for (int q = 0; q < kMgPer; q++) {
-        const int i = i0 + q;
-        if (i >= n || !active) break;
-        const float4 p_q = posm[i];
-        const MgItem it = mg_classify(s, p_q, vel[i]);
-        const int cnt[3] = {it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0};
-        if (it.keep) {
-            const float flag = mg_inside(s, it.p) ? 1.0f : 0.0f;
-            if (flag != it.v.w) vel[i].w = flag;
-            if (it.p.y != p_q.y || it.p.z != p_q.z) posm[i] = it.p; // wrapped into the periodic box
-        } else if (it.dies) {
-            posm[i].w = -1.0f;
-            vel[i].w = 0.0f;
+        for (int q = 0; q < kMgPer; q++) {
+            const int i = i0 + q;
+            if (i >= n || !active) break;
+            const float4 p_q = posm[i];
+            const MgItem it = mg_classify(s, p_q, vel[i]);
+            const int cnt[3] = {it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0};
+            if (it.keep) {
+                const float flag = mg_inside(s, it.p) ? 1.0f : 0.0f;
+                if (flag != it.v.w) vel[i].w = flag;
+                if (it.p.y != p_q.y || it.p.z != p_q.z) posm[i] = it.p; // wrapped into the periodic box
+            } else if (it.dies) {
+                posm[i].w = -1.0f;
+                vel[i].w = 0.0f;
+            }
+            for (int img = 0; img < cnt[0]; img++) {
+                const int dst = n + off[0] + img;
+                if (dst >= out_capacity) break;
+                posm[dst] = mg_image(it, img + 1, 0.0f);
+                vel[dst] = make_float4(it.v.x, it.v.y, it.v.z, 0.0f);
+            }
+            for (int img = 0; img < cnt[1]; img++) {
+                if (off[1] + img >= cap_left) break;
+                float4 w = mg_image(it, img, s.shift_left);
+                // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
+                if (s.shift_left != 0.0f && it.p.x < s.lo) w.x = fminf(w.x, nextafterf(s.lo + s.shift_left, -INFINITY));
+                msg_left[2 + 2 * (off[1] + img)] = w;
+                msg_left[3 + 2 * (off[1] + img)] = it.v;
+            }
+            for (int img = 0; img < cnt[2]; img++) {
+                if (off[2] + img >= cap_right) break;
+                float4 w = mg_image(it, img, s.shift_right);
+                if (s.shift_right != 0.0f && it.p.x >= s.hi) w.x = fmaxf(w.x, s.hi + s.shift_right);
+                msg_right[2 + 2 * (off[2] + img)] = w;
+                msg_right[3 + 2 * (off[2] + img)] = it.v;
+            }
+            off[0] += cnt[0]; off[1] += cnt[1]; off[2] += cnt[2];
         }
-        for (int img = 0; img < cnt[0]; img++) {
-            const int dst = n + off[0] + img;
-            if (dst >= out_capacity) break;
-            posm[dst] = mg_image(it, img + 1, 0.0f);
-            vel[dst] = make_float4(it.v.x, it.v.y, it.v.z, 0.0f);
-        }
-        for (int img = 0; img < cnt[1]; img++) {
-            if (off[1] + img >= cap_left) break;
-            float4 w = mg_image(it, img, s.shift_left);
-            // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
-            if (s.shift_left != 0.0f && it.p.x < s.lo) w.x = fminf(w.x, nextafterf(s.lo + s.shift_left, -INFINITY));
-            msg_left[2 + 2 * (off[1] + img)] = w;
-            msg_left[3 + 2 * (off[1] + img)] = it.v;
-        }
-        for (int img = 0; img < cnt[2]; img++) {
-            if (off[2] + img >= cap_right) break;
-            float4 w = mg_image(it, img, s.shift_right);
-            if (s.shift_right != 0.0f && it.p.x >= s.hi) w.x = fmaxf(w.x, s.hi + s.shift_right);
-            msg_right[2 + 2 * (off[2] + img)] = w;
-            msg_right[3 + 2 * (off[2] + img)] = it.v;
-        }
-        off[0] += cnt[0]; off[1] += cnt[1]; off[2] += cnt[2];
+        __syncthreads(); // the block scan's shared words are reused by the next tile
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) { // headers: count, capacity
         if (msg_left) msg_left[0] = make_float4(__int_as_float(s.has_left ? totals[1] : 0), __int_as_float(cap_left), 0.0f, 0.0f);
@@ -303,6 +319,22 @@ __global__ void __launch_bounds__(256) k_mg_append(Slab s, const float4* __restr
         posm_out[base + r] = p;
         vel_out[base + r] = make_float4(v.x, v.y, v.z, mg_inside(s, p) ? 1.0f : 0.0f);
     }
+}
+
+// After both appends: publish the new record count for the kernels of the next step (counts[0], read by the sort when the host
+// does not wait for it) and a status record the host fetches WITHOUT waiting for it (sphb_mg_unpack_async / sphb_mg_poll):
+// {records before the messages, from left, from right, total, dead among them, sent left, sent right, flags}
+// flags: 1 = the left neighbour overflowed its message, 2 = the right one did, 4 = the arrays are full.
+__global__ void k_mg_commit(const int* __restrict__ totals, const int* __restrict__ recv, int capacity, int* __restrict__ counts, int* __restrict__ status) {
+    if (threadIdx.x || blockIdx.x) return;
+    const long long kept = totals[0], cl = recv[0], cr = recv[1], total = kept + cl + cr;
+    int flags = 0;
+    if (recv[2] > recv[0]) flags |= 1;
+    if (recv[3] > recv[1]) flags |= 2;
+    if (total > capacity) flags |= 4;
+    counts[0] = (int)(total > capacity ? capacity : total);
+    status[0] = (int)kept; status[1] = (int)cl; status[2] = (int)cr; status[3] = counts[0];
+    status[4] = totals[3]; status[5] = totals[1]; status[6] = totals[2]; status[7] = flags;
 }
 
 } // namespace sphb

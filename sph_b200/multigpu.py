@@ -141,22 +141,49 @@ class SlabRank:
         # Counts drift by well under a per cent per step; a message that would not fit is reported by unpack.
         self.adaptive = True
         self.out_left = self.out_right = self.in_left = self.in_right = self.capacity
+        # After the first exchange the unpack no longer waits for the GPU (sphb_mg_unpack_async): its counts reach the host one
+        # call late -- read at the start of the next step, when they have long arrived -- which is still before the next pack
+        # needs them for the message limits, so both ends of a link keep deriving the same limits from the same exchange.
+        self.use_async = True
+        self.exchanges = 0
+        self.status_pending = False
 
     def _limit(self, last: int) -> int:
         return min(self.capacity, int(last * 1.5) + 4096) if self.adaptive else self.capacity
 
     def pack(self):
+        self.poll()     # the message limits come from the last exchange's counts
         s = self.slab
         self.engine.mg_pack_limits(s, self.send_left.data_ptr() if s.has_left else None, self.out_left,
                                    self.send_right.data_ptr() if s.has_right else None, self.out_right)
 
-    def unpack(self):
-        s = self.slab
-        self.counts = self.engine.mg_unpack(s, self.recv_left.data_ptr() if s.has_left else None,
-                                            self.recv_right.data_ptr() if s.has_right else None)
-        sent = self.engine.mg_sent()
+    def _adopt(self, counts, sent):
+        self.counts = tuple(counts)
         self.out_left, self.out_right = self._limit(sent[0]), self._limit(sent[1])
         self.in_left, self.in_right = self._limit(self.counts[1]), self._limit(self.counts[2])
+
+    def poll(self):
+        """Adopt the counts of the last asynchronous unpack (no-op if there is none outstanding)."""
+        if self.status_pending:
+            st = self.engine.mg_poll(True)
+            self._adopt(st[:4], st[5:7])
+            self.status_pending = False
+
+    def unpack(self, sync=None):
+        """Append the received messages.  The first exchange reads its counts back (they size everything that follows); later ones
+        do not wait for the GPU unless sync=True (or use_async is off): call poll() before the next pack, as step() does."""
+        s = self.slab
+        ptrs = (self.recv_left.data_ptr() if s.has_left else None, self.recv_right.data_ptr() if s.has_right else None)
+        if sync is None:
+            sync = not (self.use_async and self.exchanges >= 1)
+        self.exchanges += 1
+        if sync:
+            self.poll()
+            counts = self.engine.mg_unpack(s, *ptrs)
+            self._adopt(counts, self.engine.mg_sent())
+        else:
+            self.engine.mg_unpack_async(s, *ptrs)
+            self.status_pending = True
         return self.counts
 
     def exchange_distributed(self, dist, left, right):
@@ -166,6 +193,7 @@ class SlabRank:
             exchange(dist, self.send_left, self.send_right, self.recv_left, self.recv_right, left, right, nbytes)
 
     def step(self, dist=None, left=None, right=None):
+        self.poll()
         self.pack()
         if dist is not None:
             self.exchange_distributed(dist, left, right)
@@ -352,12 +380,13 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
     parts = np.zeros(3)
     nb = 4
     for _ in range(nb):
+        sr.poll()
         ev[0].record(sr.stream)
         sr.pack()
         ev[1].record(sr.stream)
         sr.exchange_distributed(xdist, left, right)
         ev[2].record(sr.stream)
-        sr.unpack()
+        sr.unpack(sync=True)
         ev[3].record(sr.stream)
         eng.step(1)
         since_reset[0] += 1

@@ -21,7 +21,7 @@ def run_single(ps, walls, steps):
     return posm, vel
 
 
-def run_slabs(ps, walls, steps, world, bounds, halo):
+def run_slabs(ps, walls, steps, world, bounds, halo, use_async=True):
     ranks = []
     for r in range(world):
         slab = multigpu.make_slab(r, world, bounds, halo)
@@ -31,16 +31,20 @@ def run_slabs(ps, walls, steps, world, bounds, halo):
         e.reserve(2 * len(ps))          # own + last step's ghosts (dead until the next sort) + the new ones
         e.upload(own)
         ranks.append(multigpu.SlabRank(e, slab, capacity=len(ps), device_index=0))
+        ranks[-1].use_async = use_async
     history = []
     for _ in range(steps):
         for r in ranks:
+            r.poll()            # counts of the previous (asynchronous) unpack, one call late
             r.pack()
         multigpu.exchange_in_process(ranks)
         for r in ranks:
-            r.unpack()
-        history.append([r.counts for r in ranks])
+            r.unpack()          # first exchange reads its counts back, later ones do not wait for the GPU
         for r in ranks:
             r.engine.step(1)
+        for r in ranks:
+            r.poll()
+        history.append([r.counts for r in ranks])
     owned = [r.owned() for r in ranks]
     for r in ranks:
         r.engine.close()
@@ -56,8 +60,9 @@ def match(p_a, p_b):
     return d, idx
 
 
+@pytest.mark.parametrize("use_async", [True, False])
 @pytest.mark.parametrize("world,stressed,steps,tol", [(2, True, 1, 2e-6), (3, True, 2, 5e-6), (2, False, 10, 2e-5), (3, False, 10, 2e-5)])
-def test_slabs_match_single_engine(world, stressed, steps, tol):
+def test_slabs_match_single_engine(world, stressed, steps, tol, use_async):
     # stressed block: pressure and viscosity active from step 1, but violently unstable (chaotic) -> compared over 1-2 steps;
     # rest block drifting in +x: 10 steps, particles migrate between slabs
     ps, walls = scenes.dam_break(24, 20, 12, stressed=stressed)     # 5,760 particles
@@ -67,7 +72,7 @@ def test_slabs_match_single_engine(world, stressed, steps, tol):
     x = ps["pos"][:, 0]
     bounds = multigpu.quantile_bounds(x, world, R, float(x.min()) - 1.0, float(x.max()) + 1.0)
     p1, v1 = run_single(ps, walls, steps)
-    owned, history = run_slabs(ps, walls, steps, world, bounds, halo)
+    owned, history = run_slabs(ps, walls, steps, world, bounds, halo, use_async)
     pm = np.concatenate([o[0] for o in owned])
     vm = np.concatenate([o[1] for o in owned])
     assert len(pm) == len(ps), "particles lost or duplicated across slabs"
@@ -112,6 +117,40 @@ def test_message_overflow_is_reported():
 # periodic box (config 5; an extension -- the reference has only planes).  Oracle = the reference arithmetic
 # applied to the particles plus their periodic images (positions shifted by +-L in float, exactly what the
 # engine's ghost images are), so the comparison is again order-of-summation only.
+
+def test_overflow_in_the_asynchronous_unpack_is_reported_one_call_late():
+    ps, walls = scenes.dam_break(16, 16, 16)
+    R = multigpu.support_radius()
+    x = ps["pos"][:, 0]
+    bounds = [float(x.min()) - 1, float(np.median(x)), float(x.max()) + 1]
+    ranks = []
+    for r in range(2):
+        slab = multigpu.make_slab(r, 2, bounds, 2 * R)
+        e = sph_b200.Engine()
+        e.set_walls(walls)
+        e.reserve(2 * len(ps))
+        e.upload(ps[(x >= slab.lo) & (x < slab.hi)].copy())
+        ranks.append(multigpu.SlabRank(e, slab, capacity=len(ps), device_index=0))
+    for r in ranks:
+        r.pack()
+    multigpu.exchange_in_process(ranks)
+    for r in ranks:
+        r.unpack()                      # first exchange: synchronous, fits
+        r.engine.step(1)
+    for r in ranks:
+        r.poll()
+        r.out_left = r.out_right = r.in_left = r.in_right = 8      # both ends agree on a message that is far too small
+        r.pack()
+    multigpu.exchange_in_process(ranks)
+    ranks[0].unpack()                   # asynchronous: nothing is read back, so nothing is noticed yet
+    assert ranks[0].status_pending
+    with pytest.raises(sph_b200.SphbError, match="overflowed"):
+        ranks[0].poll()
+    with pytest.raises(sph_b200.SphbError, match="no particles uploaded"):
+        ranks[0].engine.step(1)         # the state is dropped, not silently half-updated
+    for r in ranks:
+        r.engine.close()
+
 
 def with_images(ps, box_lo, box_len, halo):
     """ps + every periodic image that lies within `halo` of the box (27-image lattice, float shifts)."""
@@ -235,6 +274,7 @@ def test_dropped_ghosts_stay_dead_until_the_next_sort():
         e.reserve(2 * len(ps))
         e.upload(ps[(x >= slab.lo) & (x < slab.hi)].copy())
         ranks.append(multigpu.SlabRank(e, slab, capacity=len(ps), device_index=0))
+        ranks[-1].use_async = False          # this test reads every exchange's counts at once
     n_own = [r.engine.count() for r in ranks]
     ghosts_prev = [0, 0]
     for step in range(3):
