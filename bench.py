@@ -366,6 +366,9 @@ def main():
                          "(default 16; 4 for the pre-compressed 64 K dam break, which explodes within a dozen steps)")
     ap.add_argument("--cell-frac", type=float, default=1.0, help="grid cell edge as a fraction of the support radius h*h (>= 0.5)")
     ap.add_argument("--cell-x-div", type=int, default=0, help="x pitch of the grid = cell / this (0 = engine default, 2)")
+    ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
+                    help="multi-GPU halo transport: p2p = the pack kernel writes into the neighbours' receive buffers over NVLink peer memory "
+                         "(CUDA IPC between the ranks, flags instead of a communication call); nccl = message buffers exchanged with NCCL send/recv")
     ap.add_argument("--quick", action="store_true", help="headline only: skip the sub-records (other configs, reference comparison, bbox mode)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -311,6 +311,36 @@ int sphb_mg_poll(sphb_engine* e, size_t status[8], int wait);
  * capacity to sphb_mg_pack; sph_b200/multigpu.py does). */
 int sphb_mg_sent(sphb_engine* e, size_t sent[2]);
 
+/* --- multi-GPU: peer-to-peer halo link --------------------------------------------------------------- */
+/* The exchange without a communication library in the data path: each rank owns a block of device memory with its four
+ * receive buffers (from the left / from the right, two of each so that consecutive steps alternate) and a few flags, the
+ * neighbours map that block (CUDA IPC between processes, plain peer access inside one process), and sphb_mg_exchange runs
+ *     wait until the neighbours have consumed what these buffers held two steps ago
+ *     pack -- the kernel writes the two messages STRAIGHT INTO the neighbours' receive buffers over NVLink
+ *     raise their "arrived" flags, wait for mine, append what arrived (as sphb_mg_unpack_async: nothing is read back)
+ *     raise their "consumed" flags
+ * all as kernels on the engine's stream; the host never waits.  Only the records that exist travel (no fixed-size transfer,
+ * no size negotiation).  Flags only grow, waits give up after ~4 s of GPU time (reported by sphb_mg_poll / the next
+ * exchange as SPHB_ERR_STATE) instead of hanging the device.  NCCL (or any other transport) remains possible through
+ * sphb_mg_pack / sphb_mg_unpack; nothing like either exists in the reference. */
+typedef struct sphb_mg_link sphb_mg_link;
+#define SPHB_MG_EXPORT_BYTES 64
+
+/* Allocate the block for messages of up to `capacity` particles per neighbour and step, on the engine's GPU.  Create the
+ * link AFTER sphb_reserve / the first upload: it also allocates the exchange's scratch for the arrays' current capacity, so that
+ * sphb_mg_exchange itself allocates nothing (an allocation can wait for the whole device, which a flag wait may be holding). */
+int sphb_mg_link_create(sphb_engine* e, size_t capacity, sphb_mg_link** out);
+void sphb_mg_link_destroy(sphb_mg_link* l);
+/* A handle other PROCESSES can open (cudaIpcMemHandle_t, zero padded): send it to the two neighbour ranks. */
+int sphb_mg_link_export(sphb_mg_link* l, unsigned char handle[SPHB_MG_EXPORT_BYTES]);
+/* Connect to the neighbours' blocks from their exported handles (NULL = no neighbour on that side). */
+int sphb_mg_link_connect_ipc(sphb_mg_link* l, const unsigned char* left, const unsigned char* right);
+/* The same inside ONE process (one host driving several GPUs): the neighbours' links themselves; peer access between the
+ * devices is enabled here.  A lone rank in a periodic box passes its own link on both sides. */
+int sphb_mg_link_connect_local(sphb_mg_link* l, sphb_mg_link* left, sphb_mg_link* right);
+/* One halo exchange (see above); follow it with sphb_step(e, 1).  All ranks of a chain must call it the same number of times. */
+int sphb_mg_exchange(sphb_engine* e, sphb_mg_link* l, const sphb_slab* slab);
+
 /* --- allocation-free bounding box ------------------------------------------------------------------ */
 
 /* Largest point count sphb_bbox_noalloc accepts (its scratch is a fixed array inside the library). */

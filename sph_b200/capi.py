@@ -26,6 +26,7 @@ SPHERE = np.dtype([("pos", "<f4", 3), ("vel", "<f4", 3), ("accel", "<f4", 3), ("
 F_POS, F_VEL, F_ACCEL, F_DENSITY, F_ALL = 1, 2, 4, 8, 15
 DOMAIN_BBOX, DOMAIN_FIXED = 0, 1
 NOALLOC_MAX_POINTS = 4194304   # SPHB_NOALLOC_MAX_POINTS
+MG_EXPORT_BYTES = 64            # SPHB_MG_EXPORT_BYTES
 
 
 class SphbError(RuntimeError):
@@ -76,7 +77,8 @@ EXPORTS = [
     "sphb_host_register", "sphb_host_unregister", "sphb_eval_kernels", "sphb_get_cells", "sphb_get_bbox",
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
-    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats", "sphb_mg_unpack_async", "sphb_mg_poll",
+    "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats", "sphb_mg_unpack_async", "sphb_mg_poll", "sphb_mg_link_create", "sphb_mg_link_destroy", "sphb_mg_link_export",
+    "sphb_mg_link_connect_ipc", "sphb_mg_link_connect_local", "sphb_mg_exchange",
 ]
 
 _lib = None
@@ -146,6 +148,13 @@ def load_library() -> C.CDLL:
     L.sphb_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.sphb_mg_unpack_async.argtypes = [vp, C.POINTER(Slab), vp, vp]
     L.sphb_mg_poll.argtypes = [vp, C.POINTER(sz * 8), i32]
+    L.sphb_mg_link_create.argtypes = [vp, sz, C.POINTER(vp)]
+    L.sphb_mg_link_destroy.argtypes = [vp]
+    L.sphb_mg_link_destroy.restype = None
+    L.sphb_mg_link_export.argtypes = [vp, C.c_char_p]
+    L.sphb_mg_link_connect_ipc.argtypes = [vp, C.c_char_p, C.c_char_p]
+    L.sphb_mg_link_connect_local.argtypes = [vp, vp, vp]
+    L.sphb_mg_exchange.argtypes = [vp, vp, C.POINTER(Slab)]
     _lib = L
     return L
 
@@ -305,6 +314,29 @@ class Engine:
         st = (C.c_size_t * 8)()
         self._check(self.lib.sphb_mg_poll(self.h, C.byref(st), int(wait)))
         return tuple(int(x) for x in st)
+
+    # --- peer-to-peer halo link
+    def mg_link_create(self, capacity: int) -> int:
+        h = C.c_void_p()
+        self._check(self.lib.sphb_mg_link_create(self.h, capacity, C.byref(h)))
+        return h.value
+
+    def mg_link_destroy(self, link: int):
+        self.lib.sphb_mg_link_destroy(C.c_void_p(link))
+
+    def mg_link_export(self, link: int) -> bytes:
+        buf = C.create_string_buffer(MG_EXPORT_BYTES)
+        self._check(self.lib.sphb_mg_link_export(C.c_void_p(link), buf))
+        return buf.raw
+
+    def mg_link_connect_ipc(self, link: int, left: bytes | None, right: bytes | None):
+        self._check(self.lib.sphb_mg_link_connect_ipc(C.c_void_p(link), left, right))
+
+    def mg_link_connect_local(self, link: int, left: int | None, right: int | None):
+        self._check(self.lib.sphb_mg_link_connect_local(C.c_void_p(link), C.c_void_p(left) if left else None, C.c_void_p(right) if right else None))
+
+    def mg_exchange(self, link: int, slab: Slab):
+        self._check(self.lib.sphb_mg_exchange(self.h, C.c_void_p(link), C.byref(slab)))
 
     def mg_sent(self):
         sent = (C.c_size_t * 2)()

@@ -382,6 +382,10 @@ int poll_status(sphb_engine* e, bool wait) {
         e->have_state = false;
         return fail(SPHB_ERR_CAPACITY, "the particle arrays overflowed in the last exchange: call sphb_reserve with more room (the state is dropped)");
     }
+    if (h[7] & 8) {
+        e->have_state = false;
+        return fail(SPHB_ERR_STATE, "a neighbour never signalled on the peer-to-peer halo link (4 s): its process or GPU is gone; the state is dropped");
+    }
     return SPHB_OK;
 }
 
@@ -1171,16 +1175,56 @@ Slab to_slab(const sphb_slab* slab) {
 }
 } // namespace
 
-extern "C" int sphb_mg_unpack_async(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right) {
-    int rc = check_ready_hot(e);
-    if (rc) return rc;
-    if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
-    if (!e->mg_pending) return fail(SPHB_ERR_STATE, "sphb_mg_unpack_async without sphb_mg_pack");
+namespace {
+int unpack_async_impl(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, const int* link_err);
+
+// With CUDA's lazy module loading the FIRST launch of a kernel loads it, and that can wait for the whole device -- which never
+// comes back if a stream of this device (or, with one host thread driving several GPUs, the stream the neighbour is waiting
+// for) sits in a flag wait.  So every kernel the exchange -> step loop launches is loaded here, once per device, up front.
+int preload_hot_kernels() {
+#define PRELOAD(f)                                      \
+    do {                                                \
+        cudaFuncAttributes a_;                          \
+        CK(cudaFuncGetAttributes(&a_, f));              \
+    } while (0)
+    PRELOAD(k_link_set); PRELOAD(k_link_wait); PRELOAD(k_mg_count); PRELOAD(k_mg_scan); PRELOAD(k_mg_write); PRELOAD(k_mg_append); PRELOAD(k_mg_commit);
+    PRELOAD(k_grid_setup); PRELOAD(k_key_hist); PRELOAD(k_scan_reduce); PRELOAD(k_scan_top); PRELOAD(k_scan_apply); PRELOAD(k_row_groups);
+    PRELOAD(k_scatter); PRELOAD(k_rank_gather<false>); PRELOAD(k_sort_small<false>); PRELOAD(k_bbox_reset); PRELOAD(k_bbox); PRELOAD(k_fill_iota);
+    PRELOAD((k_density<true, true>)); PRELOAD((k_density<true, true, 1, true>));
+    PRELOAD((k_force<true, false, true, 9, true>)); PRELOAD((k_force<true, false, false, 9, true>));
+    PRELOAD((k_force<true, false, true, 9, true, 1, true>)); PRELOAD((k_force<true, false, false, 9, true, 1, true>));
+    PRELOAD((k_force<true, true, true, 9, true>)); PRELOAD((k_force<true, true, false, 9, true>));
+    PRELOAD((k_force<true, true, true, 9, true, 1, true>)); PRELOAD((k_force<true, true, false, 9, true, 1, true>));
+#undef PRELOAD
+    return SPHB_OK;
+}
+
+// Everything the exchange allocates, allocated now: cudaMalloc / cudaMallocHost may wait for the whole device, which must not
+// happen once a stream of this device sits in a flag wait of the peer-to-peer link.
+int prepare_exchange(sphb_engine* e) {
     if (!e->h_status) {
         CK(cudaMallocHost((void**)&e->h_status, 16 * sizeof(int)));
         memset(e->h_status, 0, 16 * sizeof(int));
         for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&e->ev_status[k], cudaEventDisableTiming));
     }
+    const size_t cap = e->posm[0].cap ? e->posm[0].cap : 1;
+    const size_t nb_layout = (cap + kMgTile - 1) / kMgTile;
+    CK(e->mg_counts.reserve((size_t)kMgStreams * nb_layout + 16 + 2 * nb_layout));
+    return SPHB_OK;
+}
+}
+
+extern "C" int sphb_mg_unpack_async(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right) {
+    return unpack_async_impl(e, slab, from_left, from_right, nullptr);
+}
+
+namespace {
+int unpack_async_impl(sphb_engine* e, const sphb_slab* slab, const void* from_left, const void* from_right, const int* link_err) {
+    int rc = check_ready_hot(e);
+    if (rc) return rc;
+    if (!slab) return fail(SPHB_ERR_INVALID, "null slab");
+    if (!e->mg_pending) return fail(SPHB_ERR_STATE, "sphb_mg_unpack_async without sphb_mg_pack");
+    if ((rc = prepare_exchange(e))) return rc;
     const Slab s = to_slab(slab);
     const int cur = e->cur;
     int* totals = e->mg_counts.p + kMgStreams * e->mg_blocks;
@@ -1189,7 +1233,7 @@ extern "C" int sphb_mg_unpack_async(sphb_engine* e, const sphb_slab* slab, const
     CK(cudaMemsetAsync(recv, 0, 4 * sizeof(int), e->stream));
     if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, cap, recv);
     if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, cap, recv);
-    LAUNCH(e, k_mg_commit, 1, 32, 0, totals, recv, cap, e->d_cnt, e->d_status);
+    LAUNCH(e, k_mg_commit, 1, 32, 0, totals, recv, cap, e->d_cnt, e->d_status, link_err);
     CK(cudaGetLastError());
     const int slot = (int)(e->status_issued & 1);
     CK(cudaMemcpyAsync(e->h_status + 8 * slot, e->d_status, 8 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
@@ -1212,6 +1256,7 @@ extern "C" int sphb_mg_unpack_async(sphb_engine* e, const sphb_slab* slab, const
     e->aos_valid = false;
     return SPHB_OK;
 }
+} // namespace
 
 extern "C" int sphb_mg_poll(sphb_engine* e, size_t status[8], int wait) {
     if (!e || !status) return fail(SPHB_ERR_INVALID, "null argument");
@@ -1272,6 +1317,151 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     e->box_records = 0;
     e->aos_valid = false;
     if (counts) { counts[0] = (size_t)kept; counts[1] = (size_t)cl; counts[2] = (size_t)cr; counts[3] = (size_t)total; }
+    return SPHB_OK;
+}
+
+// =====================================================================================================
+// Peer-to-peer halo link (include/sphb200.h: sphb_mg_link_*, sphb_mg_exchange)
+
+struct sphb_mg_link {
+    sphb_engine* e = nullptr;
+    size_t capacity = 0;
+    size_t buf_bytes = 0;      // one receive buffer
+    char* block = nullptr;     // [flags 256 B][recv_left[0]][recv_left[1]][recv_right[0]][recv_right[1]] on e's device
+    char* left = nullptr;      // the neighbours' blocks as seen from e's device (peer mapping), or this link's own block
+    char* right = nullptr;
+    bool left_ipc = false, right_ipc = false;
+    long long step = 0;
+};
+
+namespace {
+inline int* link_flags(char* block) { return (int*)block; }
+inline char* link_buf(const sphb_mg_link* l, char* block, int side /*0 = recv_left, 1 = recv_right*/, int parity) {
+    return block + kLinkFlagInts * sizeof(int) + (size_t)(2 * side + parity) * l->buf_bytes;
+}
+} // namespace
+
+extern "C" int sphb_mg_link_create(sphb_engine* e, size_t capacity, sphb_mg_link** out) {
+    if (!e || !out) return fail(SPHB_ERR_INVALID, "null argument");
+    if (capacity == 0 || capacity > 0x3fffffffu) return fail(SPHB_ERR_INVALID, "bad link capacity");
+    int rc = use_device(e);
+    if (rc) return rc;
+    sphb_mg_link* l = new (std::nothrow) sphb_mg_link();
+    if (!l) return fail(SPHB_ERR_INVALID, "out of host memory");
+    l->e = e;
+    l->capacity = capacity;
+    l->buf_bytes = (sphb_mg_message_bytes(capacity) + 255) & ~(size_t)255;
+    const size_t bytes = kLinkFlagInts * sizeof(int) + 4 * l->buf_bytes;
+    cudaError_t err = cudaMalloc((void**)&l->block, bytes);
+    if (err == cudaSuccess) err = cudaMemset(l->block, 0, bytes); // flags at 0, headers say "0 records"
+    if (err != cudaSuccess) {
+        if (l->block) cudaFree(l->block);
+        delete l;
+        return fail(SPHB_ERR_CUDA, "link allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(err));
+    }
+    if ((rc = preload_hot_kernels()) || (rc = prepare_exchange(e))) { // with the arrays as reserved / uploaded so far
+        cudaFree(l->block);
+        delete l;
+        return rc;
+    }
+    *out = l;
+    return SPHB_OK;
+}
+
+extern "C" void sphb_mg_link_destroy(sphb_mg_link* l) {
+    if (!l) return;
+    cudaSetDevice(l->e->device);
+    cudaStreamSynchronize(l->e->stream);
+    if (l->left && l->left_ipc) cudaIpcCloseMemHandle(l->left);
+    if (l->right && l->right_ipc && l->right != l->left) cudaIpcCloseMemHandle(l->right);
+    if (l->block) cudaFree(l->block);
+    delete l;
+}
+
+extern "C" int sphb_mg_link_export(sphb_mg_link* l, unsigned char handle[SPHB_MG_EXPORT_BYTES]) {
+    if (!l || !handle) return fail(SPHB_ERR_INVALID, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) <= SPHB_MG_EXPORT_BYTES, "export record too small");
+    CK(cudaSetDevice(l->e->device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, l->block));
+    memset(handle, 0, SPHB_MG_EXPORT_BYTES);
+    memcpy(handle, &h, sizeof h);
+    return SPHB_OK;
+}
+
+extern "C" int sphb_mg_link_connect_ipc(sphb_mg_link* l, const unsigned char* left, const unsigned char* right) {
+    if (!l) return fail(SPHB_ERR_INVALID, "null link");
+    CK(cudaSetDevice(l->e->device));
+    const unsigned char* hs[2] = {left, right};
+    char** dst[2] = {&l->left, &l->right};
+    bool* ipc[2] = {&l->left_ipc, &l->right_ipc};
+    for (int k = 0; k < 2; k++) {
+        if (!hs[k]) continue;
+        if (k == 1 && left && memcmp(left, right, sizeof(cudaIpcMemHandle_t)) == 0) { // two ranks in a ring: both neighbours are the same block
+            l->right = l->left;
+            l->right_ipc = false;
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, hs[k], sizeof h);
+        void* p = nullptr;
+        CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        *dst[k] = (char*)p;
+        *ipc[k] = true;
+    }
+    return SPHB_OK;
+}
+
+extern "C" int sphb_mg_link_connect_local(sphb_mg_link* l, sphb_mg_link* left, sphb_mg_link* right) {
+    if (!l) return fail(SPHB_ERR_INVALID, "null link");
+    CK(cudaSetDevice(l->e->device));
+    sphb_mg_link* nb[2] = {left, right};
+    for (int k = 0; k < 2; k++) {
+        if (!nb[k]) continue;
+        if (nb[k]->capacity != l->capacity) return fail(SPHB_ERR_INVALID, "links of one chain must share their capacity");
+        const int peer = nb[k]->e->device;
+        if (peer != l->e->device) {
+            int can = 0;
+            CK(cudaDeviceCanAccessPeer(&can, l->e->device, peer));
+            if (!can) return fail(SPHB_ERR_CUDA, "device %d cannot access device %d's memory", l->e->device, peer);
+            cudaError_t err = cudaDeviceEnablePeerAccess(peer, 0);
+            if (err == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else CK(err);
+        }
+    }
+    l->left = left ? left->block : nullptr;
+    l->right = right ? right->block : nullptr;
+    l->left_ipc = l->right_ipc = false;
+    return SPHB_OK;
+}
+
+extern "C" int sphb_mg_exchange(sphb_engine* e, sphb_mg_link* l, const sphb_slab* slab) {
+    int rc = check_ready_hot(e);
+    if (rc) return rc;
+    if (!l || !slab) return fail(SPHB_ERR_INVALID, "null argument");
+    if (l->e != e) return fail(SPHB_ERR_INVALID, "the link belongs to another engine");
+    if ((slab->has_left && !l->left) || (slab->has_right && !l->right)) return fail(SPHB_ERR_STATE, "the link is not connected on a side the slab has a neighbour on");
+    if ((rc = prepare_exchange(e))) return rc; // nothing below may allocate
+    const long long s = l->step;
+    const int p = (int)(s & 1);
+    int* mine = link_flags(l->block);
+    const bool hl = slab->has_left != 0, hr = slab->has_right != 0;
+    // 1. the neighbours must have consumed what was written into these buffers two steps ago
+    if (s >= 2) LAUNCH(e, k_link_wait, 1, 32, 0, hl ? mine + kLinkConsumedLeft : nullptr, (int)(s - 1), hr ? mine + kLinkConsumedRight : nullptr, (int)(s - 1), mine + kLinkError);
+    // 2. pack straight into their receive buffers: my message to the left neighbour is what it receives from its right, and vice versa
+    char* to_left = hl ? link_buf(l, l->left, 1, p) : nullptr;
+    char* to_right = hr ? link_buf(l, l->right, 0, p) : nullptr;
+    if ((rc = sphb_mg_pack_limits(e, slab, to_left, l->capacity, to_right, l->capacity))) return rc;
+    // 3. tell them it is there
+    LAUNCH(e, k_link_set, 1, 32, 0, hl ? link_flags(l->left) + kLinkArrivedRight : nullptr, (int)(s + 1), hr ? link_flags(l->right) + kLinkArrivedLeft : nullptr, (int)(s + 1));
+    // 4. wait for theirs
+    LAUNCH(e, k_link_wait, 1, 32, 0, hl ? mine + kLinkArrivedLeft : nullptr, (int)(s + 1), hr ? mine + kLinkArrivedRight : nullptr, (int)(s + 1), mine + kLinkError);
+    // 5. append (nothing is read back: counts and verdict arrive one call late, sphb_mg_poll)
+    if ((rc = unpack_async_impl(e, slab, hl ? link_buf(l, l->block, 0, p) : nullptr, hr ? link_buf(l, l->block, 1, p) : nullptr, mine + kLinkError))) return rc;
+    // 6. their buffers of this parity may be reused
+    LAUNCH(e, k_link_set, 1, 32, 0, hl ? link_flags(l->left) + kLinkConsumedRight : nullptr, (int)(s + 1), hr ? link_flags(l->right) + kLinkConsumedLeft : nullptr, (int)(s + 1));
+    CK(cudaGetLastError());
+    l->step = s + 1;
     return SPHB_OK;
 }
 

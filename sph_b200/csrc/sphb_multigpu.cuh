@@ -321,14 +321,49 @@ __global__ void __launch_bounds__(256) k_mg_append(Slab s, const float4* __restr
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Peer-to-peer halo link (sphb_mg_link): messages are written by k_mg_write straight into the NEIGHBOUR's receive buffer over
+// NVLink, so the only other traffic is a handful of 4-byte flags.  A flag lives in the memory of the GPU that waits on it and is
+// set remotely by the GPU it waits for; values only grow (the step number + 1), so a late or repeated set is harmless.
+constexpr int kLinkArrivedLeft = 0, kLinkArrivedRight = 1, kLinkConsumedLeft = 2, kLinkConsumedRight = 3, kLinkError = 4;
+constexpr int kLinkFlagInts = 64; // 256-byte flag block in front of the receive buffers
+
+// release: everything this stream did before (the pack kernel's remote stores) is visible before the flag is
+__global__ void k_link_set(int* f0, int v0, int* f1, int v1) {
+    if (threadIdx.x || blockIdx.x) return;
+    __threadfence_system();
+    if (f0) *((volatile int*)f0) = v0;
+    if (f1) *((volatile int*)f1) = v1;
+}
+
+// acquire: spin (one thread) until both flags have reached their values; gives up after ~4 s of GPU time and raises the
+// link's error flag instead of hanging the device if a neighbour died
+__global__ void k_link_wait(const int* f0, int v0, const int* f1, int v1, int* err) {
+    if (threadIdx.x || blockIdx.x) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        const bool ok0 = !f0 || *((volatile const int*)f0) >= v0;
+        const bool ok1 = !f1 || *((volatile const int*)f1) >= v1;
+        if (ok0 && ok1) break;
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > 4000000000ull) { *((volatile int*)err) = 1; break; }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
 // After both appends: publish the new record count for the kernels of the next step (counts[0], read by the sort when the host
 // does not wait for it) and a status record the host fetches WITHOUT waiting for it (sphb_mg_unpack_async / sphb_mg_poll):
 // {records before the messages, from left, from right, total, dead among them, sent left, sent right, flags}
-// flags: 1 = the left neighbour overflowed its message, 2 = the right one did, 4 = the arrays are full.
-__global__ void k_mg_commit(const int* __restrict__ totals, const int* __restrict__ recv, int capacity, int* __restrict__ counts, int* __restrict__ status) {
+// flags: 1 = the left neighbour overflowed its message, 2 = the right one did, 4 = the arrays are full, 8 = a link wait timed out.
+__global__ void k_mg_commit(const int* __restrict__ totals, const int* __restrict__ recv, int capacity, int* __restrict__ counts, int* __restrict__ status,
+                            const int* __restrict__ link_err) {
     if (threadIdx.x || blockIdx.x) return;
     const long long kept = totals[0], cl = recv[0], cr = recv[1], total = kept + cl + cr;
     int flags = 0;
+    if (link_err && *((volatile const int*)link_err)) flags |= 8; // a wait on the peer-to-peer link timed out
     if (recv[2] > recv[0]) flags |= 1;
     if (recv[3] > recv[1]) flags |= 2;
     if (total > capacity) flags |= 4;

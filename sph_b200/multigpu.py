@@ -119,19 +119,29 @@ def exchange(dist, send_left, send_right, recv_left, recv_right, left, right, nb
 
 
 class SlabRank:
-    """One rank's engine plus its message buffers."""
+    """One rank's engine plus its halo transport.
 
-    def __init__(self, engine: capi.Engine, slab: capi.Slab, capacity: int, device_index: int):
+    transport "nccl": four message buffers here, exchanged with torch.distributed point-to-point (NCCL over NVLink).
+    transport "p2p":  a sphb_mg_link -- the pack kernel writes straight into the neighbours' receive buffers (peer memory over
+                      NVLink), flags instead of a communication call; connect() wires the links up (CUDA IPC handles gathered with
+                      torch.distributed between processes, or connect_local() for several ranks living in one process)."""
+
+    def __init__(self, engine: capi.Engine, slab: capi.Slab, capacity: int, device_index: int, transport: str = "nccl"):
         import torch
         self.torch = torch
         self.engine = engine
         self.slab = slab
         self.capacity = int(capacity)
-        nbytes = int(engine.lib.sphb_mg_message_bytes(self.capacity))
+        self.transport = transport
+        self.link = None
         dev = torch.device("cuda", device_index)
-        mk = lambda: torch.zeros(nbytes, dtype=torch.uint8, device=dev)
-        self.send_left, self.send_right, self.recv_left, self.recv_right = mk(), mk(), mk(), mk()
         self.stream = torch.cuda.ExternalStream(engine.stream(), device=dev)
+        if transport == "p2p":
+            self.link = engine.mg_link_create(self.capacity)
+        else:
+            nbytes = int(engine.lib.sphb_mg_message_bytes(self.capacity))
+            mk = lambda: torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+            self.send_left, self.send_right, self.recv_left, self.recv_right = mk(), mk(), mk(), mk()
         self.counts = (0, 0, 0, 0)
         # Records each of the four messages may carry in the NEXT exchange.  The buffers are sized for the worst case
         # (capacity), but sending them whole every step costs more than the step's compute once slabs get thin
@@ -147,6 +157,29 @@ class SlabRank:
         self.use_async = True
         self.exchanges = 0
         self.status_pending = False
+
+    # --- peer-to-peer link wiring
+    def connect(self, dist, rank, world, left, right):
+        """Between processes: everybody publishes its link's IPC handle, then opens its two neighbours'."""
+        mine = self.engine.mg_link_export(self.link)
+        if world > 1:
+            handles = [None] * world
+            dist.all_gather_object(handles, mine)
+        else:
+            handles = [mine]
+        if world == 1:                 # a lone rank in a periodic box is its own neighbour: plain pointers, no IPC
+            self.engine.mg_link_connect_local(self.link, self.link if left is not None else None, self.link if right is not None else None)
+        else:
+            self.engine.mg_link_connect_ipc(self.link, handles[left] if left is not None else None, handles[right] if right is not None else None)
+
+    def connect_local(self, left_rank, right_rank):
+        """Several ranks in one process."""
+        self.engine.mg_link_connect_local(self.link, left_rank.link if left_rank is not None else None, right_rank.link if right_rank is not None else None)
+
+    def close(self):
+        if self.link is not None:
+            self.engine.mg_link_destroy(self.link)
+            self.link = None
 
     def _limit(self, last: int) -> int:
         return min(self.capacity, int(last * 1.5) + 4096) if self.adaptive else self.capacity
@@ -192,7 +225,17 @@ class SlabRank:
         with self.torch.cuda.stream(self.stream):
             exchange(dist, self.send_left, self.send_right, self.recv_left, self.recv_right, left, right, nbytes)
 
+    def exchange_p2p(self):
+        self.poll()
+        self.engine.mg_exchange(self.link, self.slab)
+        self.exchanges += 1
+        self.status_pending = True
+
     def step(self, dist=None, left=None, right=None):
+        if self.transport == "p2p":
+            self.exchange_p2p()
+            self.engine.step(1)
+            return
         self.poll()
         self.pack()
         if dist is not None:
@@ -255,7 +298,7 @@ class _Solo:
 SCALE_OF = {"drop16m": 1, "drop2m": 2, "drop256k": 4, "periodic16m": 1, "periodic2m": 2, "periodic256k": 4}
 
 
-def setup_slab_run(mode, scale, world, rank, local, accel=True):
+def setup_slab_run(mode, scale, world, rank, local, accel=True, transport="nccl", dist=None):
     """One rank's share of a slab-decomposed workload: (engine, SlabRank, own host records, neighbours, description).
     mode: "sections" = config-4 pattern, one tank section per GPU (weak); "strong" = the ONE config-4 tank cut into `world`
     slabs of equal owned-plus-ghost counts; "periodic" = config 5, a fully periodic box per GPU, `world` side by side in x."""
@@ -304,7 +347,9 @@ def setup_slab_run(mode, scale, world, rank, local, accel=True):
         eng.reserve(n_own + 4 * capacity)   # last step's ghosts stay (marked dead) until the next sort drops them
         what = (f"block drop into tank (config 4), ONE tank of {2 ** 24 // scale ** 3} particles cut into {world} x-slabs of equal owned-plus-ghost counts" if strong
                 else f"block drop into tank (config 4 pattern), one tank section of {n_own} particles per GPU ({world} sections side by side)")
-    sr = SlabRank(eng, slab, capacity, local)
+    sr = SlabRank(eng, slab, capacity, local, transport=transport)
+    if transport == "p2p":
+        sr.connect(dist, rank, world, left, right)
     return eng, sr, ps, (left, right), what, capacity
 
 
@@ -318,7 +363,8 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
     import bench as B
 
     accel = not args.no_accel
-    eng, sr, ps, (left, right), what, capacity = setup_slab_run(mode, scale, world, rank, local, accel)
+    transport = getattr(args, "transport", "nccl")
+    eng, sr, ps, (left, right), what, capacity = setup_slab_run(mode, scale, world, rank, local, accel, transport, dist)
     n_own = len(ps)
     host = torch.empty(n_own * 52, dtype=torch.uint8).pin_memory()
     host_np = host.numpy().view(capi.PARTICLE)
@@ -380,6 +426,16 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
     parts = np.zeros(3)
     nb = 4
     for _ in range(nb):
+        if transport == "p2p":           # one call: pack into the neighbours' buffers, flags, append; only the whole is timed
+            sr.poll()
+            ev[0].record(sr.stream)
+            sr.exchange_p2p()
+            ev[3].record(sr.stream)
+            eng.step(1)
+            since_reset[0] += 1
+            eng.synchronize()
+            parts += [ev[0].elapsed_time(ev[3]), 0.0, 0.0]
+            continue
         sr.poll()
         ev[0].record(sr.stream)
         sr.pack()
@@ -398,7 +454,9 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
            "ms_per_step": ms / steps, "value": value, "gpu_launches": launches_all,
            "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "engine_step_rank0": float(phase[3]),
                         "engine_step_max_over_ranks": float(step_max.item()),
-                        "breakdown_rank0": {"pack": float(parts[0]), "send_recv": float(parts[1]), "unpack": float(parts[2])}},
+                        "breakdown_rank0": ({"exchange_p2p (pack + flags + append)": float(parts[0])} if transport == "p2p" else
+                                            {"pack": float(parts[0]), "send_recv": float(parts[1]), "unpack": float(parts[2])})},
+           "transport": transport,
            "exchange_exposed_ms": ms / steps - float(step_max.item()),
            "halo": {"counts_rank0": {"kept": sr.counts[0], "from_left": sr.counts[1], "from_right": sr.counts[2]}, "message_capacity": capacity},
            "local_particles_incl_ghosts_rank0": eng.count(), "clocks": clocks, "_phase": phase}
@@ -426,6 +484,8 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
         t_e2e = float(t.item())
         out["e2e"] = {"value": total / t_e2e, "unit": B.UNIT, "h2d_bytes_per_step": expect * 52, "d2h_bytes_per_step": expect * 52,
                       "ms_per_step": 1e3 * t_e2e, "call": "per rank: sphb_upload_aos + halo exchange + sphb_step + sphb_download_aos"}
+    dist.barrier()          # nobody frees a block a neighbour may still be writing flags into
+    sr.close()
     eng.close()
     del init, host_np, host
     torch.cuda.empty_cache()
@@ -439,7 +499,7 @@ def parity_vs_single(args, world, rank, local, dist, steps=12, scale=4):
     import torch
 
     from . import scenes
-    eng, sr, ps, (left, right), _, _ = setup_slab_run("strong", scale, world, rank, local, True)
+    eng, sr, ps, (left, right), _, _ = setup_slab_run("strong", scale, world, rank, local, True, getattr(args, "transport", "nccl"), dist)
     eng.upload(ps)
     xdist = dist
     for _ in range(steps):
@@ -447,6 +507,8 @@ def parity_vs_single(args, world, rank, local, dist, steps=12, scale=4):
     posm, vel, aux = eng.download_soa()[:3]
     keep = vel[:, 3] != 0
     mine = (posm[keep], aux[keep, 0].copy())
+    dist.barrier()
+    sr.close()
     eng.close()
     gathered = [None] * world if rank == 0 else None
     if world > 1:
@@ -544,7 +606,9 @@ def bench_main(args, world, rank, local):
             "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong" if mode == "strong" else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": head["workload"], "particles": head["particles"], "particles_per_gpu": head["particles_per_gpu_rank0"],
-                       "decomposition": "x slabs, halo = 2 support radii, one NCCL send/recv pair per neighbour per step",
+                       "decomposition": "x slabs, halo = 2 support radii, one exchange with each x-neighbour per step",
+                       "transport": ("pack kernel writes into the neighbours' receive buffers over NVLink peer memory (CUDA IPC), flag kernels"
+                                     if getattr(args, "transport", "nccl") == "p2p" else "NCCL send/recv of message buffers (torch.distributed)"),
                        "l2": "state exceeds the 126 MB L2", "accel_output": not args.no_accel, "reset_every": reset},
             "clocks": head["clocks"], "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
             "phase_ms": head["phase_ms"], "exchange_exposed_ms": head["exchange_exposed_ms"], "halo": head["halo"],
