@@ -207,7 +207,8 @@ int sphb_get_stats(sphb_engine* e, sphb_stats* out);
 
 /* --- device-resident access for the headless bench and the multi-GPU driver ----------------------- */
 
-/* Upload from DEVICE SoA arrays (float4 posm = x,y,z,mass; float4 vel = vx,vy,vz,0), n particles,
+/* Upload from DEVICE SoA arrays (float4 posm = x,y,z,mass; float4 vel = vx,vy,vz,anything: the engine keeps its ownership flag
+ * there and sets it itself), n particles,
  * device-to-device on the engine's stream.  ids (may be NULL = 0..n-1) names each particle's place in the "original
  * order" that downloads return: it must be a permutation of 0..n-1.  Anything else is refused with SPHB_ERR_INVALID
  * (checked on the device; that check synchronises) and leaves the engine without a state. */

@@ -607,7 +607,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
     e->cur = 0;
     if (n) {
         CK(cudaMemcpyAsync(e->posm[0].p, posm, n * sizeof(float4), cudaMemcpyDeviceToDevice, e->stream));
-        CK(cudaMemcpyAsync(e->vel[0].p, vel, n * sizeof(float4), cudaMemcpyDeviceToDevice, e->stream));
+        LAUNCH(e, k_copy_vel_owned, cdiv(n, 256), 256, 0, (const float4*)vel, e->vel[0].p, (int)n); // w = 1: owned (0 would mean "ghost of another slab")
         CK(cudaMemsetAsync(e->aux[0].p, 0, n * sizeof(float4), e->stream));
         CK(cudaMemsetAsync(e->accel[0].p, 0, n * sizeof(float4), e->stream));
         if (ids) {

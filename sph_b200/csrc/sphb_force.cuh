@@ -122,6 +122,14 @@ __device__ __forceinline__ void force_thread(const Consts& c, const GridDesc* __
         const GridDesc g = *gd;
         const float4 pi = ldg4(posm + i);
         const float4 vi = ldg4(vel + i);
+        if (kFused && vi.w == 0.0f) {
+            // a ghost (copy of a neighbouring slab's particle, multi-GPU): it is here to be somebody's neighbour; its own force and
+            // new position are its owner's business and the next exchange replaces it anyway.  Pass it through untouched.
+            posm_out[i] = pi;
+            vel_out[i] = vi;
+            if (kAccel) accel[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            return;
+        }
         const float4 ai = ldg4(aux + i);
         int cx, cy, cz;
         cell_key(g, pi.x, pi.y, pi.z, cx, cy, cz);

@@ -100,6 +100,14 @@ __global__ void __launch_bounds__(256) k_fill_iota(int* __restrict__ ids, int n)
     if (i < n) ids[i] = i;
 }
 
+// device-to-device upload of velocities: the fourth component is the engine's ownership flag, 1 for everything a caller uploads
+__global__ void __launch_bounds__(256) k_copy_vel_owned(const float4* __restrict__ src, float4* __restrict__ dst, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 v = src[i];
+    dst[i] = make_float4(v.x, v.y, v.z, 1.0f);
+}
+
 // Caller-supplied particle ids must be a permutation of 0..n-1: the downloads invert them (k_invert_perm) and the
 // stable rank orders cells by them.  seen[] must be filled with -1; bad[0] counts ids out of range or used twice.
 __global__ void __launch_bounds__(256) k_check_ids(const int* __restrict__ ids, int n, int* __restrict__ seen, unsigned int* __restrict__ bad) {
