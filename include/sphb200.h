@@ -213,6 +213,14 @@ int sphb_get_stats(sphb_engine* e, sphb_stats* out);
  * order" that downloads return: it must be a permutation of 0..n-1.  Anything else is refused with SPHB_ERR_INVALID
  * (checked on the device; that check synchronises) and leaves the engine without a state. */
 int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, const int32_t* ids, size_t n);
+/* Replace the particle ids (0..n-1 in upload order after an upload) by the caller's own labels, ids[k] for the k-th uploaded
+ * particle: any int32 values.  From then on the labels TRAVEL with the particles through the slab exchange (a message record
+ * carries its particle's label), so a driver that gave every particle of a multi-GPU run a unique label can find each one again
+ * on whichever rank it ended up (sphb_download_soa returns the labels); sphb_multi_* does exactly that.  In exchange the
+ * calls that return particles in upload order (sphb_download_aos, sphb_download_positions, sphb_render_depth) are refused for
+ * this engine until its next upload.  Without this call ids restart at the slot numbers at every exchange. */
+int sphb_set_ids(sphb_engine* e, const int32_t* ids, size_t n);
+
 /* Current device pointers (sorted order, valid until the next call that steps or uploads):
  * posm float4, vel float4, aux float4 (density, pressure, sqrt|P/rho|, 1/rho), accel float4, ids int32. */
 int sphb_get_device_state(sphb_engine* e, void** posm, void** vel, void** aux, void** accel, int32_t** ids);
@@ -341,6 +349,27 @@ int sphb_mg_link_connect_ipc(sphb_mg_link* l, const unsigned char* left, const u
 int sphb_mg_link_connect_local(sphb_mg_link* l, sphb_mg_link* left, sphb_mg_link* right);
 /* One halo exchange (see above); follow it with sphb_step(e, 1).  All ranks of a chain must call it the same number of times. */
 int sphb_mg_exchange(sphb_engine* e, sphb_mg_link* l, const sphb_slab* slab);
+
+/* --- several GPUs behind one handle ------------------------------------------------------------------- */
+/* For a C or C++ host that wants more than one GPU without writing the slab loop itself (the reference's own main.cpp is such a
+ * host: one thread, SPH/main.cpp:280-303; nothing like this exists in the reference).  One host thread, `ndev` GPUs of one
+ * box: the particles are cut into x-slabs of equal owned-plus-ghost counts at upload, every GPU gets an engine and a
+ * peer-to-peer halo link to its neighbours, and sphb_multi_step enqueues, per step, every GPU's exchange and then every GPU's
+ * fused step without ever waiting.  Particle order: downloads return the records in the order they were uploaded (every
+ * particle carries its upload index as a label through the exchanges).  The cuts stay where the upload put them; spheres
+ * and periodic boxes are not supported here.  devices == NULL means 0 .. ndev-1. */
+typedef struct sphb_multi sphb_multi;
+int sphb_multi_create(int ndev, const int* devices, const sphb_params* p, sphb_multi** out);
+void sphb_multi_destroy(sphb_multi* m);
+const char* sphb_multi_last_error(void);
+int sphb_multi_set_walls(sphb_multi* m, const void* walls, size_t count, size_t stride);
+int sphb_multi_upload_aos(sphb_multi* m, const void* particles, size_t n, size_t stride);
+int sphb_multi_step(sphb_multi* m, int nsteps);          /* asynchronous */
+int sphb_multi_synchronize(sphb_multi* m);
+int sphb_multi_download_aos(sphb_multi* m, void* particles, size_t n, size_t stride, uint32_t field_mask);
+int sphb_multi_step_aos(sphb_multi* m, void* particles, size_t n, size_t stride, int nsteps, uint32_t field_mask);
+/* ndev, per-GPU record counts (owned + ghosts; synchronises), and the ndev+1 slab cuts.  Any pointer may be NULL. */
+int sphb_multi_info(sphb_multi* m, int* ndev, size_t* owned_plus_ghosts, double* bounds);
 
 /* --- allocation-free bounding box ------------------------------------------------------------------ */
 

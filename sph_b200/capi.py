@@ -78,7 +78,8 @@ EXPORTS = [
     "sphb_count", "sphb_enable_timing", "sphb_get_timing", "sphb_launch_count", "sphb_upload_soa_device",
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
     "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats", "sphb_mg_unpack_async", "sphb_mg_poll", "sphb_mg_link_create", "sphb_mg_link_destroy", "sphb_mg_link_export",
-    "sphb_mg_link_connect_ipc", "sphb_mg_link_connect_local", "sphb_mg_exchange",
+    "sphb_mg_link_connect_ipc", "sphb_mg_link_connect_local", "sphb_mg_exchange", "sphb_set_ids", "sphb_multi_create", "sphb_multi_destroy", "sphb_multi_last_error", "sphb_multi_set_walls",
+    "sphb_multi_upload_aos", "sphb_multi_step", "sphb_multi_synchronize", "sphb_multi_download_aos", "sphb_multi_step_aos", "sphb_multi_info",
 ]
 
 _lib = None
@@ -155,6 +156,18 @@ def load_library() -> C.CDLL:
     L.sphb_mg_link_connect_ipc.argtypes = [vp, C.c_char_p, C.c_char_p]
     L.sphb_mg_link_connect_local.argtypes = [vp, vp, vp]
     L.sphb_mg_exchange.argtypes = [vp, vp, C.POINTER(Slab)]
+    L.sphb_set_ids.argtypes = [vp, vp, sz]
+    L.sphb_multi_create.argtypes = [i32, vp, C.POINTER(Params), C.POINTER(vp)]
+    L.sphb_multi_destroy.argtypes = [vp]
+    L.sphb_multi_destroy.restype = None
+    L.sphb_multi_last_error.restype = C.c_char_p
+    L.sphb_multi_set_walls.argtypes = [vp, vp, sz, sz]
+    L.sphb_multi_upload_aos.argtypes = [vp, vp, sz, sz]
+    L.sphb_multi_step.argtypes = [vp, i32]
+    L.sphb_multi_synchronize.argtypes = [vp]
+    L.sphb_multi_download_aos.argtypes = [vp, vp, sz, sz, u32]
+    L.sphb_multi_step_aos.argtypes = [vp, vp, sz, sz, i32, u32]
+    L.sphb_multi_info.argtypes = [vp, C.POINTER(i32), vp, vp]
     _lib = L
     return L
 
@@ -185,6 +198,61 @@ def _ptr(a):
     if isinstance(a, int):
         return C.c_void_p(a)
     return a.ctypes.data_as(C.c_void_p)
+
+
+class Multi:
+    """sphb_multi_*: several GPUs of one box behind one handle, driven by this one host thread."""
+
+    def __init__(self, devices, params: "Params | None" = None, **overrides):
+        self.lib = load_library()
+        self.params = params if params is not None else default_params(**overrides)
+        devs = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        self._check(self.lib.sphb_multi_create(len(devices), devs, C.byref(self.params), C.byref(h)))
+        self.h = h
+        self.ndev = len(devices)
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise SphbError(f"sphb error {rc}: {self.lib.sphb_multi_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.sphb_multi_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_walls(self, walls: np.ndarray):
+        walls = np.ascontiguousarray(walls)
+        assert walls.dtype == WALL
+        self._check(self.lib.sphb_multi_set_walls(self.h, _ptr(walls), len(walls), WALL.itemsize))
+
+    def upload(self, particles: np.ndarray):
+        assert particles.dtype == PARTICLE and particles.flags.c_contiguous
+        self._check(self.lib.sphb_multi_upload_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize))
+
+    def step(self, nsteps: int = 1):
+        self._check(self.lib.sphb_multi_step(self.h, nsteps))
+
+    def synchronize(self):
+        self._check(self.lib.sphb_multi_synchronize(self.h))
+
+    def download(self, particles: np.ndarray, mask: int = F_ALL):
+        assert particles.dtype == PARTICLE and particles.flags.c_contiguous
+        self._check(self.lib.sphb_multi_download_aos(self.h, _ptr(particles), len(particles), PARTICLE.itemsize, mask))
+        return particles
+
+    def info(self):
+        counts = (C.c_size_t * self.ndev)()
+        bounds = (C.c_double * (self.ndev + 1))()
+        nd = C.c_int(0)
+        self._check(self.lib.sphb_multi_info(self.h, C.byref(nd), counts, bounds))
+        return [int(c) for c in counts], [float(b) for b in bounds]
 
 
 class Engine:
@@ -286,6 +354,11 @@ class Engine:
     def upload_soa_device(self, posm_ptr: int, vel_ptr: int, n: int, ids_ptr: int | None = None):
         self._check(self.lib.sphb_upload_soa_device(self.h, C.c_void_p(posm_ptr), C.c_void_p(vel_ptr),
                                                     C.c_void_p(ids_ptr) if ids_ptr else None, n))
+
+    def set_ids(self, ids: np.ndarray):
+        """Caller's labels (int32, upload order); they travel with the particles through slab exchanges."""
+        ids = np.ascontiguousarray(ids, np.int32)
+        self._check(self.lib.sphb_set_ids(self.h, _ptr(ids), len(ids)))
 
     # --- multi-GPU slab decomposition
     def reserve(self, n_max: int):

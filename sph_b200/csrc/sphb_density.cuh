@@ -58,7 +58,9 @@ __device__ __forceinline__ void rank_gather_one(int p, const int2* pairs, const 
     const int b = cell_start[k], e = cell_start[k + 1];
     int rank = 0;
     if (e - b <= kStableRankLimit) {
-        for (int q = b; q < e; q++) rank += (pairs[q].x < me.x);
+        // ids are unique after an upload; after slab exchanges two records of one cell may carry the same id (ranks number their
+        // uploads independently unless told otherwise): the arrival slot breaks the tie so that the result stays a permutation
+        for (int q = b; q < e; q++) rank += (pairs[q].x < me.x) || (pairs[q].x == me.x && q < p);
     } else {
         rank = p - b; // arrival order
         if (p == b) atomicAdd(stats, 1u); // one count per such cell and sort (sphb_get_stats: arrival_order_cells)

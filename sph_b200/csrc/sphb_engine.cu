@@ -106,6 +106,8 @@ struct sphb_engine {
 
     bool have_state = false;
     bool oid_identity = false; // after sphb_mg_unpack: original id == slot; oid[cur] is only written when somebody needs it
+    bool global_ids = false;   // sphb_set_ids: ids are the caller's labels and travel with the particles through the slab exchange
+                               // (then downloads in "original order" make no sense for this engine and are refused)
     size_t n_dead = 0;       // records among the n that sphb_mg_pack marked dead (mass -1): the next sort files them last and drops them
     bool grid_valid = false; // cell_start / sorted order correspond to the current positions
     bool bbox_valid = false; // d_bbox holds the bbox of the current positions
@@ -581,6 +583,7 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    e->global_ids = false;
     e->n_dead = 0;
     e->n_deferred = false;
     e->status_seen = e->status_issued;
@@ -633,6 +636,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    e->global_ids = false;
     e->n_dead = 0;
     e->n_deferred = false;
     e->status_seen = e->status_issued;
@@ -647,9 +651,18 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
     return SPHB_OK;
 }
 
+namespace {
+int no_global_ids(sphb_engine* e, const char* what) {
+    if (e->global_ids) return fail(SPHB_ERR_STATE, "%s returns particles in upload order, which this engine does not have: its ids are the caller's labels "
+                                                   "(sphb_set_ids); use sphb_download_soa and place the records by their ids", what);
+    return SPHB_OK;
+}
+} // namespace
+
 int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask) {
     int rc = check_ready(e);
     if (rc) return rc;
+    if ((rc = no_global_ids(e, "sphb_download_aos"))) return rc;
     if (n > e->n) return fail(SPHB_ERR_INVALID, "download of %zu particles but the engine holds %zu", n, e->n);
     if (n && !particles) return fail(SPHB_ERR_INVALID, "null particles");
     if (stride < 48 || stride % 4 || stride > 128) return fail(SPHB_ERR_INVALID, "stride must be a multiple of 4 in [48, 128]");
@@ -676,6 +689,7 @@ int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, 
 int sphb_download_positions(sphb_engine* e, float* xyz, size_t n) {
     int rc = check_ready(e);
     if (rc) return rc;
+    if ((rc = no_global_ids(e, "sphb_download_positions"))) return rc;
     if (n > e->n) return fail(SPHB_ERR_INVALID, "download of %zu particles but the engine holds %zu", n, e->n);
     if (n && !xyz) return fail(SPHB_ERR_INVALID, "null output");
     if (n == 0) return SPHB_OK;
@@ -734,6 +748,7 @@ void sphb_default_camera(sphb_camera* cam) {
 int sphb_render_depth(sphb_engine* e, const sphb_camera* cam, float* image) {
     int rc = check_ready(e);
     if (rc) return rc;
+    if ((rc = no_global_ids(e, "sphb_render_depth"))) return rc;
     if (!cam || !image) return fail(SPHB_ERR_INVALID, "null argument");
     if (cam->width <= 0 || cam->height <= 0 || (long long)cam->width * cam->height > (1ll << 28)) return fail(SPHB_ERR_INVALID, "bad image size");
     Camera c;
@@ -955,6 +970,7 @@ int sphb_get_cells(sphb_engine* e, int32_t* cell_xyz, int32_t* perm, int32_t* di
     int rc = check_ready(e);
     if (rc) return rc;
     if (!e->grid_valid) return fail(SPHB_ERR_STATE, "no grid: call sphb_update_cells first");
+    if (cell_xyz && (rc = no_global_ids(e, "sphb_get_cells (cell_xyz)"))) return rc;
     const size_t n = e->n;
     GridDesc g;
     CK(cudaMemcpyAsync(&g, e->d_grid, sizeof g, cudaMemcpyDeviceToHost, e->stream));
@@ -1119,6 +1135,25 @@ extern "C" int sphb_reserve(sphb_engine* e, size_t n_max) {
     return ensure_capacity(e, n_max);
 }
 
+extern "C" int sphb_set_ids(sphb_engine* e, const int32_t* ids, size_t n) {
+    int rc = check_ready(e);
+    if (rc) return rc;
+    if (n != e->n) return fail(SPHB_ERR_INVALID, "sphb_set_ids: %zu ids for %zu particles", n, e->n);
+    if (n && !ids) return fail(SPHB_ERR_INVALID, "null ids");
+    if ((rc = ensure_oid(e))) return rc;
+    // ids arrive in ORIGINAL (upload) order; the state may already be sorted: place each through the current ids
+    CK(e->scratch.reserve(n ? n : 1));
+    int* d_ids = (int*)e->scratch.p;
+    if (n) {
+        CK(cudaMemcpyAsync(d_ids, ids, n * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+        LAUNCH(e, k_relabel, cdiv(n, 256), 256, 0, e->oid[e->cur].p, d_ids, (int)n);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(e->stream)); // ids may live on the caller's stack
+    }
+    e->global_ids = true;
+    return SPHB_OK;
+}
+
 extern "C" int sphb_mg_pack(sphb_engine* e, const sphb_slab* slab, void* msg_left, void* msg_right, size_t capacity) {
     return sphb_mg_pack_limits(e, slab, msg_left, capacity, msg_right, capacity);
 }
@@ -1149,7 +1184,10 @@ extern "C" int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* 
     const int* nd = n_dev(e);
     LAUNCH(e, k_mg_count, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, nd, nb_layout, e->mg_counts.p, touch);
     LAUNCH(e, k_mg_scan, kMgStreams, kMgScanThreads, 0, e->mg_counts.p, nb_layout, n, nd, totals);
-    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, n, nd, nb_layout, e->mg_counts.p, totals, out_cap, touch,
+    if (e->global_ids) {
+        if (int rco = ensure_oid(e)) return rco;
+    }
+    LAUNCH(e, k_mg_write, nb, kMgThreads, 0, s, e->posm[cur].p, e->vel[cur].p, e->global_ids ? e->oid[cur].p : (int*)nullptr, n, nd, nb_layout, e->mg_counts.p, totals, out_cap, touch,
            (float4*)msg_left, (float4*)msg_right, (int)cap_left, (int)cap_right);
     CK(cudaGetLastError());
     e->mg_pending = true;
@@ -1231,8 +1269,8 @@ int unpack_async_impl(sphb_engine* e, const sphb_slab* slab, const void* from_le
     int* recv = totals + 4;
     const int cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
     CK(cudaMemsetAsync(recv, 0, 4 * sizeof(int), e->stream));
-    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, cap, recv);
-    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, cap, recv);
+    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, e->global_ids ? e->oid[cur].p : (int*)nullptr, cap, recv);
+    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, e->global_ids ? e->oid[cur].p : (int*)nullptr, cap, recv);
     LAUNCH(e, k_mg_commit, 1, 32, 0, totals, recv, cap, e->d_cnt, e->d_status, link_err);
     CK(cudaGetLastError());
     const int slot = (int)(e->status_issued & 1);
@@ -1247,7 +1285,7 @@ int unpack_async_impl(sphb_engine* e, const sphb_slab* slab, const void* from_le
     e->n = est;
     e->n_deferred = true;
     e->cnt_slot = 0;
-    e->oid_identity = true; // ids restart at the slot numbers; the next sort reads them as such without an array
+    e->oid_identity = !e->global_ids; // ids restart at the slot numbers (materialised only if somebody asks), unless they are the caller's labels
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;
@@ -1284,8 +1322,8 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     int* recv = totals + 4;
     const int cap = (int)(e->posm[cur].cap < 0x7fffffffu ? e->posm[cur].cap : 0x7fffffffu);
     CK(cudaMemsetAsync(recv, 0, 4 * sizeof(int), e->stream));
-    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, cap, recv);
-    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, cap, recv);
+    if (from_left) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_left, totals, 0, e->posm[cur].p, e->vel[cur].p, e->global_ids ? e->oid[cur].p : (int*)nullptr, cap, recv);
+    if (from_right) LAUNCH(e, k_mg_append, 148 * 4, 256, 0, s, (const float4*)from_right, totals, 1, e->posm[cur].p, e->vel[cur].p, e->global_ids ? e->oid[cur].p : (int*)nullptr, cap, recv);
     CK(cudaGetLastError());
     int h[8];
     CK(cudaMemcpyAsync(h, totals, 8 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
@@ -1309,7 +1347,7 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     e->n = (size_t)total;
     e->n_deferred = false; // the count is exact again
     e->last_status[3] = (int)total;
-    e->oid_identity = true; // ids restart at the slot numbers; the next sort reads them as such without an array
+    e->oid_identity = !e->global_ids; // ids restart at the slot numbers (materialised only if somebody asks), unless they are the caller's labels
     e->grid_valid = false;
     e->mask_valid = false;
     e->vr_valid = false;

@@ -18,8 +18,8 @@ namespace sphb {
 // (kTrashBins) -- no compaction pass over the state.  The records that do move -- the two messages and the periodic
 // y/z images appended behind the current particles -- are compacted in input order with a two-level scan
 // (per-block counts -> scan -> write), so the result is deterministic.  A message is a header record {count,
-// capacity, 0...} followed by 32-byte particle records {posm float4, vel float4}; the receiver appends them and
-// sets the ownership flag itself.
+// capacity, 0...} followed by 32-byte particle records {posm float4, (vx, vy, vz, particle id as bits)}; the receiver appends
+// them, files the id in its id array and sets the ownership flag itself.
 
 struct Slab {
     float lo, hi, halo;
@@ -225,7 +225,8 @@ __global__ void __launch_bounds__(kMgScanThreads) k_mg_scan(int* __restrict__ bl
 // pass 3: write.  A kept particle stays in its slot (flag refreshed, wrapped coordinates written back); its periodic
 // images go behind the current particles (slot n + offset); a dropped one is marked dead; left/right -> messages.
 // posm/vel are read and written by the thread that owns slot i only.
-__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restrict__ posm, float4* __restrict__ vel, int n, const int* __restrict__ n_dev,
+__global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restrict__ posm, float4* __restrict__ vel, int* __restrict__ oid, int n,
+                                                         const int* __restrict__ n_dev,
                                                          int nb_layout, const int* __restrict__ block_offsets, const int* __restrict__ totals,
                                                          int out_capacity, const unsigned char* __restrict__ touch,
                                                          float4* __restrict__ msg_left, float4* __restrict__ msg_right, int cap_left, int cap_right) {
@@ -264,6 +265,10 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
             const float4 p_q = posm[i];
             const MgItem it = mg_classify(s, p_q, vel[i]);
             const int cnt[3] = {it.keep ? it.nimg - 1 : 0, it.left ? it.nimg : 0, it.right ? it.nimg : 0};
+            // the particle's id travels with it: in a message it rides in the velocity record's fourth word (the ownership
+            // flag there means nothing to the receiver, who decides ownership by position), locally it stays in the id array
+            const int id = (oid && (cnt[0] | cnt[1] | cnt[2])) ? oid[i] : 0; // oid == null: ids are not tracked across exchanges
+            const float4 v_msg = make_float4(it.v.x, it.v.y, it.v.z, __int_as_float(id));
             if (it.keep) {
                 const float flag = mg_inside(s, it.p) ? 1.0f : 0.0f;
                 if (flag != it.v.w) vel[i].w = flag;
@@ -277,6 +282,7 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
                 if (dst >= out_capacity) break;
                 posm[dst] = mg_image(it, img + 1, 0.0f);
                 vel[dst] = make_float4(it.v.x, it.v.y, it.v.z, 0.0f);
+                if (oid) oid[dst] = id;
             }
             for (int img = 0; img < cnt[1]; img++) {
                 if (off[1] + img >= cap_left) break;
@@ -284,14 +290,14 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
                 // a migrant through the periodic seam must land INSIDE the far slab even if x + period rounds up onto its face
                 if (s.shift_left != 0.0f && it.p.x < s.lo) w.x = fminf(w.x, nextafterf(s.lo + s.shift_left, -INFINITY));
                 msg_left[2 + 2 * (off[1] + img)] = w;
-                msg_left[3 + 2 * (off[1] + img)] = it.v;
+                msg_left[3 + 2 * (off[1] + img)] = v_msg;
             }
             for (int img = 0; img < cnt[2]; img++) {
                 if (off[2] + img >= cap_right) break;
                 float4 w = mg_image(it, img, s.shift_right);
                 if (s.shift_right != 0.0f && it.p.x >= s.hi) w.x = fmaxf(w.x, s.hi + s.shift_right);
                 msg_right[2 + 2 * (off[2] + img)] = w;
-                msg_right[3 + 2 * (off[2] + img)] = it.v;
+                msg_right[3 + 2 * (off[2] + img)] = v_msg;
             }
             off[0] += cnt[0]; off[1] += cnt[1]; off[2] += cnt[2];
         }
@@ -305,8 +311,8 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
 
 // append a received message behind the kept particles; counts[0] = kept, counts[1] = records already appended
 __global__ void __launch_bounds__(256) k_mg_append(Slab s, const float4* __restrict__ msg, const int* __restrict__ totals, int which,
-                                                   float4* __restrict__ posm_out, float4* __restrict__ vel_out, int out_capacity,
-                                                   int* __restrict__ recv_counts) {
+                                                   float4* __restrict__ posm_out, float4* __restrict__ vel_out, int* __restrict__ oid_out,
+                                                   int out_capacity, int* __restrict__ recv_counts) {
     const int count = min(__float_as_int(msg[0].x), __float_as_int(msg[0].y)); // an overflowing sender truncated its payload
     const int base = totals[0] + (which ? recv_counts[0] : 0);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -318,6 +324,7 @@ __global__ void __launch_bounds__(256) k_mg_append(Slab s, const float4* __restr
         const float4 p = msg[2 + 2 * r], v = msg[3 + 2 * r];
         posm_out[base + r] = p;
         vel_out[base + r] = make_float4(v.x, v.y, v.z, mg_inside(s, p) ? 1.0f : 0.0f);
+        if (oid_out) oid_out[base + r] = __float_as_int(v.w); // the sender's id for this particle (see k_mg_write)
     }
 }
 

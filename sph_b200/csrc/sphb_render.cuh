@@ -108,6 +108,12 @@ __global__ void __launch_bounds__(256) k_copy_vel_owned(const float4* __restrict
     dst[i] = make_float4(v.x, v.y, v.z, 1.0f);
 }
 
+// sphb_set_ids: replace each record's upload index by the caller's label for that index
+__global__ void __launch_bounds__(256) k_relabel(int* __restrict__ oid, const int* __restrict__ labels, int n) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) oid[p] = labels[oid[p]];
+}
+
 // Caller-supplied particle ids must be a permutation of 0..n-1: the downloads invert them (k_invert_perm) and the
 // stable rank orders cells by them.  seen[] must be filled with -1; bad[0] counts ids out of range or used twice.
 __global__ void __launch_bounds__(256) k_check_ids(const int* __restrict__ ids, int n, int* __restrict__ seen, unsigned int* __restrict__ bad) {

@@ -6,6 +6,10 @@
 // Build modes
 //   default                  includes the reference's own Particle.hpp / Wall.hpp / Sphere.hpp (and GLM)
 //   SPHB_SHIM_STANDALONE     uses sphb_records.hpp + sphb_glm_min.hpp (no reference tree needed)
+// Several GPUs
+//   use_devices(list)        before the first call: the step runs on those GPUs through sphb_multi_* (x-slabs, peer-to-peer halo
+//                            links).  The four methods then act as ONE step executed at collision() -- the only point at which
+//                            main.cpp looks at the particles (main.cpp:97-110) -- and the host vector is refreshed there.
 // Sync policy
 //   default                  every method leaves the host vector exactly as the reference would
 //                            (density/pressure after update_density, accel after update_forces, ...)
@@ -31,10 +35,10 @@
 
 class SphUtils {
 public:
-    SphUtils() : eng_(0), failed_(false), resident_(false), nwalls_(0) { sphb_default_params(&params_); }
+    SphUtils() : eng_(0), multi_(0), failed_(false), resident_(false), nwalls_(0) { sphb_default_params(&params_); }
 
     SphUtils(float nsmooth_length, float nrho0, float nc, float ndt, float nepsilon)
-        : eng_(0), failed_(false), resident_(false), nwalls_(0) {
+        : eng_(0), multi_(0), failed_(false), resident_(false), nwalls_(0) {
         // A global SphUtils is constructed before main() (main.cpp:62): no CUDA call here, only numbers.
         sphb_default_params(&params_);
         params_.h = nsmooth_length;
@@ -46,11 +50,20 @@ public:
 
     ~SphUtils() {
         if (eng_) sphb_destroy(eng_);
+        if (multi_) sphb_multi_destroy(multi_);
+    }
+
+    // Run the step on several GPUs (CUDA ordinals; the same ordinal twice puts two slabs on one GPU).  Before the first call.
+    bool use_devices(const std::vector<int>& devices) {
+        if (eng_ || multi_ || devices.empty()) return false;
+        devices_ = devices;
+        return true;
     }
 
     // Solver constants beyond the five constructor arguments, before the first call (optional).
     sphb_params& params() { return params_; }
-    sphb_engine* engine() { return ensure() ? eng_ : 0; }
+    sphb_engine* engine() { return ensure() ? eng_ : 0; }   // null when several GPUs are in use
+    bool ready() { return ensure(); }
 
     float kernel_function(glm::vec3 i, glm::vec3 j) {
         float w = 0.0f;
@@ -76,6 +89,7 @@ public:
 
     void update_density(std::vector<Particle>& particles) {
         if (particles.empty() || !ensure()) return;
+        if (multi_) return; // several GPUs: the whole step runs at collision()
         // first call of a step: the host vector is the truth (it may have grown, main.cpp:441)
         resident_ = false;
         if (!push(particles)) return;
@@ -85,6 +99,7 @@ public:
 
     void update_forces(std::vector<Particle>& particles, std::vector<Sphere>& spheres) {
         if (particles.empty() || !ensure()) return;
+        if (multi_) return;
         if (!spheres_in(spheres) || !push(particles)) return;
         if (!ok(sphb_update_forces(eng_))) return;
         pull(particles, SPHB_F_ACCEL);
@@ -93,6 +108,7 @@ public:
 
     void update_posvel(std::vector<Particle>& particles, std::vector<Sphere>& spheres) {
         if (particles.empty() || !ensure()) return;
+        if (multi_) return;
         if (!spheres_in(spheres) || !push(particles)) return;
         if (!ok(sphb_update_posvel(eng_))) return;
         pull(particles, SPHB_F_POS | SPHB_F_VEL);
@@ -101,6 +117,10 @@ public:
 
     void collision(std::vector<Particle>& particles, std::vector<Wall>& walls, std::vector<Sphere>& spheres) {
         if (particles.empty() || !ensure()) return;
+        if (multi_) {
+            step_scene(particles, walls, 1);
+            return;
+        }
         if (!set_walls(walls) || !spheres_in(spheres)) return;
         if (!push(particles)) return;
         if (!ok(sphb_collision(eng_))) return;
@@ -117,12 +137,18 @@ public:
     void step_scene(std::vector<Particle>& particles, std::vector<Wall>& walls, int nsteps = 1) {
         if (particles.empty() || !ensure() || !set_walls(walls)) return;
         resident_ = false;
+        if (multi_) {
+            mok(sphb_multi_step_aos(multi_, &particles[0], particles.size(), sizeof(Particle), nsteps, SPHB_F_ALL));
+            return;
+        }
         ok(sphb_step_aos(eng_, &particles[0], particles.size(), sizeof(Particle), nsteps, SPHB_F_ALL));
     }
 
 private:
     sphb_params params_;
     sphb_engine* eng_;
+    sphb_multi* multi_;
+    std::vector<int> devices_;
     bool failed_, resident_;
     size_t nwalls_;
     float walls_[SPHB_MAX_WALLS * 6];
@@ -136,9 +162,16 @@ private:
         failed_ = true;
         return false;
     }
+    bool mok(int rc) {
+        if (rc == SPHB_OK) return true;
+        if (!failed_) fprintf(stderr, "sphb200: %s (further calls are ignored)\n", sphb_multi_last_error());
+        failed_ = true;
+        return false;
+    }
     bool ensure() {
         if (failed_) return false;
-        if (eng_) return true;
+        if (eng_ || multi_) return true;
+        if (!devices_.empty()) return mok(sphb_multi_create((int)devices_.size(), &devices_[0], &params_, &multi_));
         return ok(sphb_create(&params_, 0, &eng_));
     }
     bool push(std::vector<Particle>& particles) {
@@ -162,6 +195,7 @@ private:
         if (n == nwalls_ && memcmp(w, walls_, n * 6 * sizeof(float)) == 0) return true;
         memcpy(walls_, w, n * 6 * sizeof(float));
         nwalls_ = n;
+        if (multi_) return mok(sphb_multi_set_walls(multi_, walls_, n, 6 * sizeof(float)));
         return ok(sphb_set_walls(eng_, walls_, n, 6 * sizeof(float)));
     }
     void eval(glm::vec3 i, glm::vec3 j, float* w, float* g, float* l) {

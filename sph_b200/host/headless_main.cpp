@@ -1,7 +1,9 @@
 // Headless driver: the reference's scene set-up and step loop (SPH/main.cpp initScene :555-559,
 // initParticles :490-505, addParticle :424-442, initWalls :508-540, step_scene :280-303) with every GL /
 // GLUT call left out, driving the engine through the drop-in SphUtils class exactly as main.cpp does.
-//   sph_headless [steps=20] [fused|methods] [emit|noemit] [picture.pgm]
+//   sph_headless [steps=20] [fused|methods] [emit|noemit] [picture.pgm] [devices=0,1]
+// "devices=a,b,..." runs the step on those GPUs (sphb_multi_*: x-slabs, peer-to-peer halo links); the same ordinal twice puts
+// two slabs on one GPU.  The picture needs the single-engine path.
 // "fused" uses SphUtils::step_scene (one sphb_step_aos call per step) instead of the four methods.
 // "emit" switches the emitter of step_scene on (main.cpp:281-290, the Enter key): one particle per step from
 // rand(), until MAX_PARTICLES -- the particle vector grows between steps and the engine follows.
@@ -87,12 +89,25 @@ static uint64_t fnv_pos() {
 }
 
 int main(int argc, char** argv) {
+    std::vector<int> devices;
+    for (int a = 1; a < argc; a++)
+        if (strncmp(argv[a], "devices=", 8) == 0) {
+            for (const char* q = argv[a] + 8; *q;) {
+                devices.push_back(atoi(q));
+                while (*q && *q != ',') q++;
+                if (*q == ',') q++;
+            }
+            for (int b = a; b + 1 < argc; b++) argv[b] = argv[b + 1];
+            argc--;
+            a--;
+        }
+    if (!devices.empty()) sph.use_devices(devices);
     int steps = argc > 1 ? atoi(argv[1]) : 20;
     bool fused = argc > 2 && strcmp(argv[2], "fused") == 0;
     generateParticles = argc > 3 && strcmp(argv[3], "emit") == 0;
     initScene();
     printf("particles %zu walls %zu\n", particles.size(), walls.size());
-    if (!sph.engine()) return 2;
+    if (!sph.ready()) return 2;
     for (int s = 1; s <= steps; s++) {
         step_scene(fused);
         if (s == 1 || s == 2 || s == 10 || s == 20 || s == 100 || s == steps) {
@@ -107,7 +122,7 @@ int main(int argc, char** argv) {
         }
     }
     const char* pgm = argc > 4 ? argv[4] : 0;
-    if (pgm) {
+    if (pgm && sph.engine()) {
         sphb_camera cam;
         sphb_default_camera(&cam);
         std::vector<float> img((size_t)cam.width * cam.height);
