@@ -87,7 +87,12 @@ typedef struct sphb_params {
                               277-278), on the full neighbourhood.  0 (default): off, as in the reference, whose call is
                               commented out (SphUtils.cpp:175).  When on, sphb_step runs the phases unfused */
     float lap_visc_coef;   /* 0.1f (SphUtils.cpp:277) */
-    int32_t reserved[4];
+    int32_t parity_mode;   /* 1 => update_density / update_forces (and sphb_step, unfused) evaluate every pair the way the reference's own
+                              loops do: neighbours in ascending original index, each float operation of SphUtils.cpp:55-79, 100-149,
+                              181-239 with its rounding, W and gradW through double -- rho, P and accel then equal the reference's BIT FOR
+                              BIT.  ~50x slower than the fast kernels: for refereeing and debugging.  0 (default): the fast kernels,
+                              equal to the reference within 1e-5 (tests/test_gpu_parity.py) */
+    int32_t reserved[3];
 } sphb_params;
 
 /* Fill *p with the reference's constants (main.cpp:30-41 and the literals of SphUtils.cpp). */

@@ -66,7 +66,7 @@ class Params(C.Structure):
         ("wall_test_off", C.c_double), ("wall_test_lim", C.c_double),
         ("domain_mode", C.c_int32), ("domain_lo", C.c_float * 3), ("domain_hi", C.c_float * 3),
         ("periodic_reserved", C.c_int32 * 3), ("max_cells", C.c_int64), ("write_accel", C.c_int32),
-        ("cell_x_div", C.c_int32), ("laplacian_viscosity", C.c_int32), ("lap_visc_coef", C.c_float), ("reserved", C.c_int32 * 4),
+        ("cell_x_div", C.c_int32), ("laplacian_viscosity", C.c_int32), ("lap_visc_coef", C.c_float), ("parity_mode", C.c_int32), ("reserved", C.c_int32 * 3),
     ]
 
 

@@ -17,3 +17,4 @@
 #include "sphb_spheres.cuh"
 #include "sphb_render.cuh"
 #include "sphb_multigpu.cuh"
+#include "sphb_parity.cuh"

@@ -337,6 +337,17 @@ int run_density(sphb_engine* e, bool with_aux) {
     return SPHB_OK;
 }
 
+ParityConsts parity_consts(const sphb_engine* e) {
+    const sphb_params& p = e->params;
+    const float pi_f = (float)3.14159265358979323846264338327950288; // glm::pi<float>()
+    ParityConsts pc;
+    const float den_f = 64 * pi_f; // int * float -> float (SphUtils.cpp:61)
+    pc.den_w = (double)den_f * pow((double)p.h, 9);
+    pc.den_g = (double)pi_f * pow((double)p.h, 6);
+    pc.eos_k = p.eos_k; pc.alpha = p.visc_alpha; pc.beta = p.visc_beta; pc.eta = p.visc_eta;
+    return pc;
+}
+
 template <bool kFused, bool kBBox, bool kAccel, bool kDerive>
 auto force_kernel(int rows) {
     return rows == 9 ? k_force<kFused, kBBox, kAccel, 9, kDerive> : k_force<kFused, kBBox, kAccel, 25, kDerive>;
@@ -442,6 +453,7 @@ void sphb_default_params(sphb_params* p) {
     p->write_accel = 1;
     p->laplacian_viscosity = 0; // the reference's call is commented out (SphUtils.cpp:175)
     p->lap_visc_coef = 0.1f;    // SphUtils.cpp:277
+    p->parity_mode = 0;
 }
 
 const char* sphb_last_error(void) { return g_err; }
@@ -785,6 +797,14 @@ int sphb_update_density(sphb_engine* e) {
     if (rc) return rc;
     if (e->n == 0) return SPHB_OK;
     if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
+    if (e->params.parity_mode) {
+        if ((rc = ensure_oid(e))) return rc;
+        LAUNCH(e, k_density_parity, cdiv(e->n, 128), 128, 0, e->c, parity_consts(e), e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->oid[e->cur].p,
+               e->aux[e->cur].p, (int)e->n);
+        CK(cudaGetLastError());
+        e->vr_valid = false;
+        return SPHB_OK;
+    }
     return run_density(e, true);
 }
 
@@ -794,6 +814,13 @@ int sphb_update_forces(sphb_engine* e) {
     if (e->nspheres) LAUNCH(e, k_sphere_forces, 1, 32, 0, e->c, e->d_spheres, e->nspheres);
     if (e->n == 0) return SPHB_OK;
     if (!e->grid_valid && (rc = run_sort(e, true))) return rc;
+    if (e->params.parity_mode) {
+        if ((rc = ensure_oid(e))) return rc;
+        LAUNCH(e, k_force_parity, cdiv(e->n, 128), 128, 0, e->c, parity_consts(e), e->d_grid, e->cell_start.p, e->posm[e->cur].p, e->vel[e->cur].p,
+               e->aux[e->cur].p, e->oid[e->cur].p, e->accel[e->cur].p, (int)e->n);
+        CK(cudaGetLastError());
+        return SPHB_OK;
+    }
     if (!e->mask_valid && (rc = run_density(e, false))) return rc;
     const int n = (int)e->n, cur = e->cur;
     // vr_valid: rho/P in aux are this engine's own (update_density ran on this sorted state) -> two-gather kernel
@@ -841,7 +868,7 @@ int sphb_collision(sphb_engine* e) {
 
 int sphb_step(sphb_engine* e, int nsteps) {
     int rc = check_ready_hot(e);
-    if (!rc && e->n_deferred && (e->nspheres || e->params.laplacian_viscosity || e->rows != 9)) rc = resolve_counts(e); // those paths size work from the host's n
+    if (!rc && e->n_deferred && (e->nspheres || e->params.laplacian_viscosity || e->params.parity_mode || e->rows != 9)) rc = resolve_counts(e); // those paths size work from the host's n
     if (rc) return rc;
     if (nsteps < 0) return fail(SPHB_ERR_INVALID, "nsteps < 0");
     if (e->n == 0) return SPHB_OK;
@@ -853,7 +880,7 @@ int sphb_step(sphb_engine* e, int nsteps) {
 #endif
     const bool bbox = SPHB_BBOX_FUSED && !e->c.domain_fixed;
     const bool acc = e->params.write_accel != 0;
-    if (e->params.laplacian_viscosity) { // optional extra force pass: run the phases one by one
+    if (e->params.laplacian_viscosity || e->params.parity_mode) { // optional extra force pass / reference-order arithmetic: run the phases one by one
         for (int s = 0; s < nsteps; s++)
             if ((rc = sphb_update_density(e)) || (rc = sphb_update_forces(e)) || (rc = sphb_update_posvel(e)) || (rc = sphb_collision(e)))
                 return rc;
