@@ -37,5 +37,36 @@ def main(path):
         print(f"  traffic = dram read + write = {rd} {ur} + {wr} {uw}")
 
 
+def hot_spots(path, top=12):
+    """Per kernel, the instructions that collect the most warp-stall samples (ncu --page source, needs --import-source on)."""
+    raw = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    kern, cur = [], None
+    for r in rows:
+        if r and r[0] == "Kernel Name":
+            cur = {"name": r[1], "hdr": None, "rows": []}
+            kern.append(cur)
+        elif cur is not None and cur["hdr"] is None:
+            cur["hdr"] = r
+        elif cur is not None:
+            cur["rows"].append(r)
+    seen = set()
+    for k in kern:
+        if k["name"] in seen or not k["rows"]:
+            continue
+        seen.add(k["name"])
+        h = k["hdr"]
+        si, ie, src, lsb = h.index("# Samples"), h.index("Instructions Executed"), h.index("Source"), h.index("stall_long_sb")
+        tot = sum(int(r[si]) for r in k["rows"])
+        toti = sum(int(r[ie]) for r in k["rows"])
+        print(f"\nhot spots: {k['name'][:90]}\n  {len(k['rows'])} SASS instructions, {tot} warp samples, {toti} warp-instructions executed")
+        idx = sorted(range(len(k["rows"])), key=lambda i: -int(k["rows"][i][si]))[:top]
+        for i in sorted(idx):
+            r = k["rows"][i]
+            print(f"  #{i:5d} {100 * int(r[si]) / max(tot, 1):5.1f} % of samples ({int(r[lsb])} long-scoreboard)  executed {int(r[ie]):9d}  {r[src].strip()[:90]}")
+
+
 if __name__ == "__main__":
     main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--hot":
+        hot_spots(sys.argv[1])

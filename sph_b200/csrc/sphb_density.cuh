@@ -139,10 +139,20 @@ __device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* c
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
-    for (int base = 0; base < nrows; base += kRgThreads) {
-        const int rho = base + threadIdx.x;
-        int v = 0;
-        if (rho < nrows) v = (cell_start[(rho + 1) * nx] - cell_start[rho * nx] + kDT - 1) / kDT;
+    // four consecutive rows per thread and round (all their loads in flight together): the block is alone on the GPU, so the
+    // number of dependent rounds is its running time (30 K rows: 51 -> see DESIGN.md)
+    constexpr int kPer = 4;
+    for (int base = 0; base < nrows; base += kRgThreads * kPer) {
+        const int rho0 = base + threadIdx.x * kPer;
+        int b[kPer + 1];
+#pragma unroll
+        for (int q = 0; q <= kPer; q++) b[q] = cell_start[min(rho0 + q, nrows) * nx];
+        int vq[kPer], v = 0;
+#pragma unroll
+        for (int q = 0; q < kPer; q++) {
+            vq[q] = rho0 + q < nrows ? (b[q + 1] - b[q] + kDT - 1) / kDT : 0;
+            v += vq[q];
+        }
         int inc = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -162,10 +172,14 @@ __device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* c
         }
         __syncthreads();
         const int carry = s_carry;
-        const int ex = carry + (warp ? s_warp[warp - 1] : 0) + inc - v;
-        if (rho < nrows) gstart[rho] = ex;
+        int ex = carry + (warp ? s_warp[warp - 1] : 0) + inc - v;
+#pragma unroll
+        for (int q = 0; q < kPer; q++) {
+            if (rho0 + q < nrows) gstart[rho0 + q] = ex;
+            ex += vq[q];
+        }
         __syncthreads();
-        if (threadIdx.x == kRgThreads - 1) s_carry = ex + v;
+        if (threadIdx.x == kRgThreads - 1) s_carry = ex;
         __syncthreads();
     }
     if (threadIdx.x == 0) gstart[nrows] = s_carry;

@@ -83,6 +83,7 @@ struct sphb_engine {
     int mg_blocks = 0;
     size_t mg_sent[2] = {0, 0}; // records the last pack put (wanted to put) into its left / right message, known after unpack
     bool mg_pending = false; // sphb_mg_pack ran, sphb_mg_unpack has not committed yet
+    bool mg_used = false;    // this engine has exchanged slabs since its last upload: its arrays may hold ghosts
     size_t reserved = 0;
     GridDesc* d_grid = nullptr;
     BBoxAcc* d_bbox = nullptr;
@@ -595,6 +596,7 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    e->mg_used = false;
     e->global_ids = false;
     e->n_dead = 0;
     e->n_deferred = false;
@@ -648,6 +650,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    e->mg_used = false;
     e->global_ids = false;
     e->n_dead = 0;
     e->n_deferred = false;
@@ -905,12 +908,16 @@ int sphb_step(sphb_engine* e, int nsteps) {
         if (n <= kSmallScene && e->rows == 9 && !e->n_deferred) // small scene: four neighbours in flight per thread (latency, not throughput)
             kfn = bbox ? (acc ? k_force<true, true, true, 9, true, 4> : k_force<true, true, false, 9, true, 4>)
                        : (acc ? k_force<true, false, true, 9, true, 4> : k_force<true, false, false, 9, true, 4>);
+        // an engine that exchanges slabs holds ghosts: the variant that passes them through (big scenes, 9-row stencil, no bbox fold)
+        const bool ghosts = e->mg_used && e->rows == 9 && !bbox && (n > kSmallScene || e->n_deferred);
+        if (ghosts) kfn = acc ? k_force<true, false, true, 9, true, 1, false, true> : k_force<true, false, false, 9, true, 1, false, true>;
         LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS, 0);
         int box_records = bbox ? blocks * 4 : 0;
         if (e->n_deferred) { // n was an estimate: a few blocks walk whatever particles lie beyond the main launch (normally none)
             constexpr int kTail = 148;
             auto ktail = bbox ? (acc ? k_force<true, true, true, 9, true, 1, true> : k_force<true, true, false, 9, true, 1, true>)
                               : (acc ? k_force<true, false, true, 9, true, 1, true> : k_force<true, false, false, 9, true, 1, true>);
+            if (ghosts) ktail = acc ? k_force<true, false, true, 9, true, 1, true, true> : k_force<true, false, false, 9, true, 1, true, true>;
             LAUNCH(e, ktail, kTail, 128, 0, FORCE_ARGS, blocks * 128);
             if (bbox) box_records += kTail * 4;
         }
@@ -1218,6 +1225,7 @@ extern "C" int sphb_mg_pack_limits(sphb_engine* e, const sphb_slab* slab, void* 
            (float4*)msg_left, (float4*)msg_right, (int)cap_left, (int)cap_right);
     CK(cudaGetLastError());
     e->mg_pending = true;
+    e->mg_used = true;
     return SPHB_OK;
 }
 
@@ -1258,6 +1266,8 @@ int preload_hot_kernels() {
     PRELOAD((k_density<true, true>)); PRELOAD((k_density<true, true, 1, true>));
     PRELOAD((k_force<true, false, true, 9, true>)); PRELOAD((k_force<true, false, false, 9, true>));
     PRELOAD((k_force<true, false, true, 9, true, 1, true>)); PRELOAD((k_force<true, false, false, 9, true, 1, true>));
+    PRELOAD((k_force<true, false, true, 9, true, 1, false, true>)); PRELOAD((k_force<true, false, false, 9, true, 1, false, true>));
+    PRELOAD((k_force<true, false, true, 9, true, 1, true, true>)); PRELOAD((k_force<true, false, false, 9, true, 1, true, true>));
     PRELOAD((k_force<true, true, true, 9, true>)); PRELOAD((k_force<true, true, false, 9, true>));
     PRELOAD((k_force<true, true, true, 9, true, 1, true>)); PRELOAD((k_force<true, true, false, 9, true, 1, true>));
 #undef PRELOAD

@@ -97,7 +97,7 @@ __device__ __forceinline__ void collide_walls(const Consts& c, float4& p, float4
 // kIlp:   neighbours fetched per iteration.  1 for real workloads (more only cost registers there); 4 for small scenes,
 //         where a handful of warps per SM hide nothing and a thread's chain of L2-latency gathers IS the kernel time:
 //         four neighbours' records are requested before the first is used.  Same accumulation order, same bits.
-template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp>
+template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp, bool kGhosts>
 __device__ __forceinline__ void force_thread(const Consts& c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                              const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
                                              const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
@@ -122,9 +122,10 @@ __device__ __forceinline__ void force_thread(const Consts& c, const GridDesc* __
         const GridDesc g = *gd;
         const float4 pi = ldg4(posm + i);
         const float4 vi = ldg4(vel + i);
-        if (kFused && vi.w == 0.0f) {
+        if (kFused && kGhosts && vi.w == 0.0f) {
             // a ghost (copy of a neighbouring slab's particle, multi-GPU): it is here to be somebody's neighbour; its own force and
             // new position are its owner's business and the next exchange replaces it anyway.  Pass it through untouched.
+            // (kGhosts: only engines that exchange slabs run this variant -- on one GPU the test alone cost 1.5 %.)
             posm_out[i] = pi;
             vel_out[i] = vi;
             if (kAccel) accel[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -299,7 +300,7 @@ __device__ __forceinline__ void force_thread(const Consts& c, const GridDesc* __
 // warp_box[global warp id] (8 floats: min xyz, -, max xyz, -); k_bbox_fold joins them at the start of the next sort.  (Folding
 // into ONE global box from here -- per block behind a barrier, or per warp -- cost 0.36 / 0.5 ms at 16.7 M: the barrier keeps
 // blocks resident for their slowest warp, and half a million warps polling one L2 line queue up behind each other.)
-template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp = 1, bool kLoop = false>
+template <bool kFused, bool kBBox, bool kAccel, int kRows, bool kDerive, int kIlp = 1, bool kLoop = false, bool kGhosts = false>
 __global__ void __launch_bounds__(128, (kRows == 9 && kIlp == 1) ? SPHB_FORCE_MINBLOCKS : 1) k_force(Consts c, const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
                                                const float4* __restrict__ posm, const float4* __restrict__ vel, const float4* __restrict__ aux,
                                                const float4* __restrict__ vr, const unsigned int* __restrict__ mask,
@@ -308,11 +309,11 @@ __global__ void __launch_bounds__(128, (kRows == 9 && kIlp == 1) ? SPHB_FORCE_MI
     if (n_dev) n = *n_dev;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     if (!kLoop) {
-        force_thread<kFused, kBBox, kAccel, kRows, kDerive, kIlp>(c, gd, cell_start, posm, vel, aux, vr, mask, accel, posm_out, vel_out, n, ms,
+        force_thread<kFused, kBBox, kAccel, kRows, kDerive, kIlp, kGhosts>(c, gd, cell_start, posm, vel, aux, vr, mask, accel, posm_out, vel_out, n, ms,
                                                                   first + blockIdx.x * blockDim.x + threadIdx.x, lo, hi);
     } else {
         for (long long base = first + (long long)blockIdx.x * blockDim.x; base < n; base += (long long)gridDim.x * blockDim.x)
-            force_thread<kFused, kBBox, kAccel, kRows, kDerive, kIlp>(c, gd, cell_start, posm, vel, aux, vr, mask, accel, posm_out, vel_out, n, ms,
+            force_thread<kFused, kBBox, kAccel, kRows, kDerive, kIlp, kGhosts>(c, gd, cell_start, posm, vel, aux, vr, mask, accel, posm_out, vel_out, n, ms,
                                                                       (int)base + (int)threadIdx.x, lo, hi);
     }
     if (kFused && kBBox) {
