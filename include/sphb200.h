@@ -244,13 +244,19 @@ void* sphb_stream(sphb_engine* e);
  * sprite square gets N.xy = 2 (s,t) - 1 with (s,t) = 1/2 + (pixel centre - window centre) / edge (origin lower
  * left, main.cpp:565), is discarded if |N.xy|^2 > 1, else N.z = sqrt(1 - |N.xy|^2) and
  * value = clamp((MVP (pos + sprite_radius N, 1)).z / .w, 0, 1).  No depth buffer is requested by the viewer
- * (GLUT_DOUBLE | GLUT_RGB, main.cpp:730), so a later particle overwrites an earlier one: particle order decides. */
+ * (GLUT_DOUBLE | GLUT_RGB, main.cpp:730), so by default a later particle overwrites an earlier one: particle order decides
+ * (sphb_camera.depth_test = 1 gives the other possible outcome, see there). */
 typedef struct sphb_camera {
     float mvp[16];        /* column-major, like glm::mat4 / glUniformMatrix4fv(..., GL_FALSE, ...) */
     int32_t width, height;
     float point_scale;    /* 50   (sph.vertexshader:10) */
     float sprite_radius;  /* 0.1  (sph.fragmentshader:19) */
     float clear_value;    /* 1.0  (glClearColor(1,1,1,1), main.cpp:230) */
+    int32_t depth_test;   /* 0 (default): no depth buffer -- the viewer asks for GLUT_DOUBLE | GLUT_RGB (main.cpp:730), so the particle drawn
+                             last wins a pixel.  1: as if the visual carried depth bits after all: glEnable(GL_DEPTH_TEST), GL_LESS
+                             (main.cpp:567-571) then make the sprite with the smallest point depth (clip.z / clip.w + 1) / 2 win, the
+                             first drawn on a tie (the fragment shader writes no gl_FragDepth).  Which of the two a real GL
+                             implementation shows is its choice of visual; both are available here */
 } sphb_camera;
 
 /* main.cpp:48-60: perspective(45.0f [radians in GLM 0.9.6], 4/3, 0.1, 100) * lookAt((0,-0.8,1.5), (0,-0.8,0),

@@ -181,10 +181,10 @@ class Oracle:
         self.lib.orc_default_mvp(_vp(m))
         return m
 
-    def render_depth(self, ps, mvp, width=1080, height=920, point_scale=50.0, sprite_radius=0.1, clear_value=1.0):
+    def render_depth(self, ps, mvp, width=1080, height=920, point_scale=50.0, sprite_radius=0.1, clear_value=1.0, depth_test=0):
         img = np.zeros((height, width), np.float32)
-        self.lib.orc_render_depth(_vp(np.ascontiguousarray(ps)), C.c_size_t(len(ps)), _f3(mvp), C.c_int(width), C.c_int(height),
-                                  C.c_float(point_scale), C.c_float(sprite_radius), C.c_float(clear_value), _vp(img))
+        self.lib.orc_render_depth2(_vp(np.ascontiguousarray(ps)), C.c_size_t(len(ps)), _f3(mvp), C.c_int(width), C.c_int(height),
+                                   C.c_float(point_scale), C.c_float(sprite_radius), C.c_float(clear_value), C.c_int(depth_test), _vp(img))
         return img
 
     # --- scene (main.cpp:424-540)

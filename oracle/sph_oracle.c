@@ -730,8 +730,17 @@ static void mvp_apply(const float m[16], float x, float y, float z, float out[4]
 }
 
 /* particles in order, later ones overwrite (no depth buffer, main.cpp:730); image[h][w], row 0 at the bottom */
-void orc_render_depth(const orc_particle* ps, size_t n, const float mvp[16], int width, int height, float point_scale,
-                      float sprite_radius, float clear_value, float* image) {
+/* depth_test = 0: no depth buffer, a later particle overwrites an earlier one (what GLUT_DOUBLE | GLUT_RGB asks for,
+ * main.cpp:730).  depth_test = 1: the visual happens to carry depth bits, so glEnable(GL_DEPTH_TEST) / glDepthFunc(GL_LESS)
+ * (main.cpp:567-571) act: the fragment shader does not write gl_FragDepth, so every fragment of a sprite has the depth of the
+ * point itself, (clip.z / clip.w + 1) / 2, and the sprite with the smallest one wins a pixel (the first drawn on a tie). */
+void orc_render_depth2(const orc_particle* ps, size_t n, const float mvp[16], int width, int height, float point_scale,
+                       float sprite_radius, float clear_value, int depth_test, float* image) {
+    float* zbuf = NULL;
+    if (depth_test) {
+        zbuf = (float*)malloc(sizeof(float) * (size_t)width * height);
+        for (long i = 0; i < (long)width * height; i++) zbuf[i] = 1.0f; /* glClear(GL_DEPTH_BUFFER_BIT) */
+    }
     for (long i = 0; i < (long)width * height; i++) image[i] = clear_value;
     for (size_t k = 0; k < n; k++) {
         float clip[4];
@@ -760,7 +769,18 @@ void orc_render_depth(const orc_particle* ps, size_t n, const float mvp[16], int
                 float depth = cp[2] / cp[3];
                 if (depth < 0.0f) depth = 0.0f;
                 if (depth > 1.0f) depth = 1.0f;
+                if (zbuf) {
+                    float zwin = clip[2] / clip[3] * 0.5f + 0.5f;
+                    if (!(zwin < zbuf[(size_t)py * width + px])) continue; /* GL_LESS */
+                    zbuf[(size_t)py * width + px] = zwin;
+                }
                 image[(size_t)py * width + px] = depth;
             }
     }
+    free(zbuf);
+}
+
+void orc_render_depth(const orc_particle* ps, size_t n, const float mvp[16], int width, int height, float point_scale,
+                      float sprite_radius, float clear_value, float* image) {
+    orc_render_depth2(ps, n, mvp, width, height, point_scale, sprite_radius, clear_value, 0, image);
 }

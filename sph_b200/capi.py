@@ -37,7 +37,7 @@ class Camera(C.Structure):
     """struct sphb_camera (include/sphb200.h)."""
 
     _fields_ = [("mvp", C.c_float * 16), ("width", C.c_int32), ("height", C.c_int32), ("point_scale", C.c_float),
-                ("sprite_radius", C.c_float), ("clear_value", C.c_float)]
+                ("sprite_radius", C.c_float), ("clear_value", C.c_float), ("depth_test", C.c_int32)]
 
 
 class Slab(C.Structure):

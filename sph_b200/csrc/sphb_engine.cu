@@ -770,18 +770,26 @@ int sphb_render_depth(sphb_engine* e, const sphb_camera* cam, float* image) {
     memcpy(c.m, cam->mvp, sizeof c.m);
     c.width = cam->width; c.height = cam->height;
     c.point_scale = cam->point_scale; c.sprite_radius = cam->sprite_radius; c.clear_value = cam->clear_value;
+    c.depth_test = cam->depth_test != 0;
     const size_t npix = (size_t)c.width * c.height;
     const int n = (int)e->n, cur = e->cur;
-    CK(e->scratch.reserve(2 * npix));
-    unsigned int* winner = (unsigned int*)e->scratch.p;
-    float* d_img = e->scratch.p + npix;
-    CK(cudaMemsetAsync(winner, 0, npix * sizeof(unsigned int), e->stream));
+    CK(e->scratch.reserve(3 * npix));
+    float* d_img = e->scratch.p + 2 * npix;
     if (n) {
         if (int rco = ensure_oid(e)) return rco;
         LAUNCH(e, k_invert_perm, cdiv(n, 256), 256, 0, e->oid[cur].p, e->inv.p, n);
-        LAUNCH(e, k_splat_winner, cdiv((long long)n * 32, 256), 256, 0, c, e->posm[cur].p, e->inv.p, n, winner);
     }
-    LAUNCH(e, k_splat_shade, cdiv(npix, 256), 256, 0, c, e->posm[cur].p, e->inv.p, winner, d_img);
+    if (c.depth_test) {
+        unsigned long long* winner = (unsigned long long*)e->scratch.p;
+        CK(cudaMemsetAsync(winner, 0xff, npix * sizeof(unsigned long long), e->stream));
+        if (n) LAUNCH(e, k_splat_winner_depth, cdiv((long long)n * 32, 256), 256, 0, c, e->posm[cur].p, e->inv.p, n, winner);
+        LAUNCH(e, k_splat_shade_depth, cdiv(npix, 256), 256, 0, c, e->posm[cur].p, e->inv.p, winner, d_img);
+    } else {
+        unsigned int* winner = (unsigned int*)e->scratch.p;
+        CK(cudaMemsetAsync(winner, 0, npix * sizeof(unsigned int), e->stream));
+        if (n) LAUNCH(e, k_splat_winner, cdiv((long long)n * 32, 256), 256, 0, c, e->posm[cur].p, e->inv.p, n, winner);
+        LAUNCH(e, k_splat_shade, cdiv(npix, 256), 256, 0, c, e->posm[cur].p, e->inv.p, winner, d_img);
+    }
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(image, d_img, npix * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));

@@ -15,6 +15,7 @@ struct Camera {
     float m[16]; // column-major
     int width, height;
     float point_scale, sprite_radius, clear_value;
+    int depth_test; // 1: the sprite with the smallest point depth wins a pixel (GL_LESS, first drawn on a tie); 0: the last drawn
 };
 
 __device__ __forceinline__ float4 mvp_mul(const Camera& c, float x, float y, float z) {
@@ -63,6 +64,44 @@ __global__ void __launch_bounds__(256) k_splat_winner(Camera c, const float4* __
         float d;
         if (sprite_fragment(c, p, xw, yw, edge, px, py, d)) atomicMax(winner + (size_t)py * c.width + px, (unsigned int)o + 1u);
     }
+}
+
+// depth-tested variant: the key (point depth, particle index) is minimised, so the nearest sprite wins and the lowest index on a tie
+__global__ void __launch_bounds__(256) k_splat_winner_depth(Camera c, const float4* __restrict__ posm, const int* __restrict__ inv, int n,
+                                                            unsigned long long* __restrict__ winner) {
+    const int o = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (o >= n) return;
+    const float4 p = posm[inv[o]];
+    float xw, yw, edge;
+    if (!sprite_of(c, p, xw, yw, edge)) return;
+    const float4 clip = mvp_mul(c, p.x, p.y, p.z);
+    const float zwin = clip.z / clip.w * 0.5f + 0.5f;
+    if (!(zwin < 1.0f)) return; // GL_LESS against the cleared depth 1
+    const unsigned long long key = ((unsigned long long)f2ord(zwin) << 32) | (unsigned int)o;
+    const int x0 = max(0, (int)floorf(xw - 0.5f * edge)), x1 = min(c.width - 1, (int)ceilf(xw + 0.5f * edge));
+    const int y0 = max(0, (int)floorf(yw - 0.5f * edge)), y1 = min(c.height - 1, (int)ceilf(yw + 0.5f * edge));
+    const int wx = x1 - x0 + 1, wy = y1 - y0 + 1;
+    if (wx <= 0 || wy <= 0) return;
+    for (int k = lane; k < wx * wy; k += 32) {
+        const int px = x0 + k % wx, py = y0 + k / wx;
+        float d;
+        if (sprite_fragment(c, p, xw, yw, edge, px, py, d)) atomicMin(winner + (size_t)py * c.width + px, key);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_splat_shade_depth(Camera c, const float4* __restrict__ posm, const int* __restrict__ inv,
+                                                           const unsigned long long* __restrict__ winner, float* __restrict__ image) {
+    const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= c.width * c.height) return;
+    const unsigned long long w = winner[pix];
+    float v = c.clear_value;
+    if (w != ~0ull) {
+        const float4 p = posm[inv[(unsigned int)w]];
+        float xw, yw, edge, d;
+        if (sprite_of(c, p, xw, yw, edge) && sprite_fragment(c, p, xw, yw, edge, pix % c.width, pix / c.width, d)) v = d;
+    }
+    image[pix] = v;
 }
 
 __global__ void __launch_bounds__(256) k_splat_shade(Camera c, const float4* __restrict__ posm, const int* __restrict__ inv,

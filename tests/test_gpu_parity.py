@@ -656,6 +656,14 @@ def test_splat_renderer_matches_cpu_restatement(eng, oracle):
     differ = np.abs(got - want) > 1e-5
     assert differ.sum() <= 1e-3 * covered.sum(), f"{differ.sum()} of {covered.sum()} covered pixels differ"   # sprite-edge ties only
     assert np.array_equal(got == 1.0, want == 1.0) or differ.sum() <= 1e-3 * covered.sum()
+    # the other outcome a GL implementation may show: a visual with depth bits, GL_LESS on the points' own depths (main.cpp:567-571)
+    cam.depth_test = 1
+    got_z = eng.render_depth(cam)
+    want_z = oracle.render_depth(ps, np.array(cam.mvp[:], np.float32), cam.width, cam.height, depth_test=1)
+    differ_z = np.abs(got_z - want_z) > 1e-5
+    assert differ_z.sum() <= 1e-3 * covered.sum(), f"{differ_z.sum()} of {covered.sum()} covered pixels differ with the depth test on"
+    assert np.array_equal(got_z == 1.0, got == 1.0)                     # same coverage, other winners
+    assert (np.abs(got_z - got) > 1e-5).sum() > 0.01 * covered.sum()     # the two rules really give different pictures
 
 
 def test_headless_cpp_driver_writes_the_viewer_picture(tmp_path):
