@@ -131,8 +131,10 @@ int sphb_get_spheres(sphb_engine* e, void* spheres, size_t count, size_t stride)
  * (main.cpp:441 grows the vector).  Particle order is remembered: downloads return it. */
 int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stride);
 
-/* Device SoA -> host AoS, original order, only the fields in field_mask are written.  n may be smaller than
- * sphb_count: the first n particles of the original order are returned. */
+/* Device SoA -> host AoS, original order, only the fields in field_mask are taken from the engine.  n may be smaller than
+ * sphb_count: the first n particles of the original order are returned.  The records are rebuilt from the engine's copy of the
+ * last upload plus the masked fields, so a field OUTSIDE the mask keeps the value it had at that upload: if the host has edited
+ * such a field since, upload again before relying on it (with no upload to go by, the host records are fetched first). */
 int sphb_download_aos(sphb_engine* e, void* particles, size_t n, size_t stride, uint32_t field_mask);
 
 /* Positions only, packed x,y,z (12 B per particle), original order: what the viewer's update_positions() copies into

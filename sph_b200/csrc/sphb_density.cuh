@@ -130,7 +130,8 @@ constexpr int kDT = 4;
 constexpr int kRgThreads = 1024;
 
 // the work of one block of kRgThreads threads (k_row_groups, and one phase of k_sort_small)
-__device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* cell_start, int* gstart, int* counts) {
+template <int kPer>
+__device__ __forceinline__ void row_groups_impl(int nx, int nrows, const int* cell_start, int* gstart, int* counts) {
     // counts[1] = particles in real cells = the live count after this sort (records filed in the trash bins excluded):
     // what the kernels after the sort use as n when the host does not know it (sphb_mg_unpack_async)
     if (threadIdx.x == 0 && counts) counts[1] = cell_start[nx * nrows];
@@ -139,9 +140,8 @@ __device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* c
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
-    // four consecutive rows per thread and round (all their loads in flight together): the block is alone on the GPU, so the
-    // number of dependent rounds is its running time (30 K rows: 51 -> see DESIGN.md)
-    constexpr int kPer = 4;
+    // kPer consecutive rows per thread and round (all their loads in flight together): the block is alone on the GPU, so the
+    // number of dependent rounds is its running time (30 K rows, four per thread: 51 -> 36 us)
     for (int base = 0; base < nrows; base += kRgThreads * kPer) {
         const int rho0 = base + threadIdx.x * kPer;
         int b[kPer + 1];
@@ -183,6 +183,11 @@ __device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* c
         __syncthreads();
     }
     if (threadIdx.x == 0) gstart[nrows] = s_carry;
+}
+
+__device__ __forceinline__ void row_groups_block(int nx, int nrows, const int* cell_start, int* gstart, int* counts) {
+    if (nrows > kRgThreads) row_groups_impl<4>(nx, nrows, cell_start, gstart, counts);
+    else row_groups_impl<1>(nx, nrows, cell_start, gstart, counts); // small grids: one round either way, fewer loads
 }
 
 __global__ void __launch_bounds__(kRgThreads) k_row_groups(const GridDesc* __restrict__ gd, const int* __restrict__ cell_start,
@@ -534,16 +539,29 @@ __global__ void __launch_bounds__(kRgThreads) k_sort_small(Consts c, BBoxAcc* ac
     __shared__ GridDesc s_g;
     __shared__ int s_scan[32];
     const int tid = threadIdx.x;
+    if (rearm_bbox) { // bounding-box grid mode and no box at hand: take it here (SphUtils.cpp:11-23) rather than in two launches of its own
+        if (tid < 3) {
+            acc->lo[tid] = f2ord(INFINITY);
+            acc->hi[tid] = f2ord(-INFINITY);
+        }
+        __syncthreads();
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (int i = tid; i < n; i += kRgThreads) {
+            const float4 p = ldg4(posm_in + i);
+            lo[0] = fminf(lo[0], p.x); hi[0] = fmaxf(hi[0], p.x);
+            lo[1] = fminf(lo[1], p.y); hi[1] = fmaxf(hi[1], p.y);
+            lo[2] = fminf(lo[2], p.z); hi[2] = fmaxf(hi[2], p.z);
+        }
+        bbox_block_commit(lo, hi, acc);
+        __threadfence_block();
+        __syncthreads();
+    }
     if (tid == 0) {
         derive_grid(c, acc, s_g);
         *gd = s_g;
     }
     __syncthreads();
     const GridDesc g = s_g;
-    if (rearm_bbox && tid < 3) { // after derive_grid has read the box: re-arm it for this step's force kernel
-        acc->lo[tid] = f2ord(INFINITY);
-        acc->hi[tid] = f2ord(-INFINITY);
-    }
     for (int i = tid; i <= g.nbins; i += kRgThreads) cell_start[i] = 0;
     __syncthreads();
     for (int i = tid; i < n; i += kRgThreads) { // K1

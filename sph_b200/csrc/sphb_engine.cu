@@ -266,17 +266,19 @@ int finish_sort(sphb_engine* e, int nxt) {
 // K0..K3: grid description, keys, stable counting sort, reorder into the other ping-pong buffer.
 int run_sort(sphb_engine* e, bool carry_all) {
     const int n = (int)e->n;
+    const bool small = n <= kSmallSort;
+    bool box_in_sort = false;
     if (!e->c.domain_fixed) {
-        int rc = ensure_bbox(e);
-        if (rc) return rc;
+        if (small && !e->bbox_valid && e->box_records == 0) box_in_sort = true; // the single-block sort takes the box itself
+        else if (int rc = ensure_bbox(e)) return rc;
     }
     const int cur = e->cur, nxt = cur ^ 1;
     const int ntile_cap = cdiv(e->max_cells + 1 + kTrashBins, kScanTile);
     int setup_blocks = cdiv(e->max_cells + 1 + kTrashBins, 256 * 8);
     if (setup_blocks > 148 * 8) setup_blocks = 148 * 8;
-    if (n <= kSmallSort) { // small scene: the eight kernels below as phases of one single-block launch (same functions)
+    if (small) { // small scene: the eight kernels below as phases of one single-block launch (same functions)
         const int* oid_in = e->oid_identity ? (const int*)nullptr : e->oid[cur].p;
-        const int rearm = 0, trash = (e->n_dead || e->n_deferred) ? 1 : 0;
+        const int rearm = box_in_sort ? 1 : 0, trash = (e->n_dead || e->n_deferred) ? 1 : 0;
 #define SMALL_ARGS e->c, e->d_bbox, e->d_grid, e->cell_start.p, e->row_groups.p, e->key.p, e->slot.p, e->pairs.p, oid_in, e->posm[cur].p, \
                    e->vel[cur].p, e->aux[cur].p, e->accel[cur].p, e->posm[nxt].p, e->vel[nxt].p, e->aux[nxt].p, e->accel[nxt].p, e->oid[nxt].p, n, \
                    n_dev(e), e->d_cnt, rearm, trash, e->d_stats
@@ -284,6 +286,7 @@ int run_sort(sphb_engine* e, bool carry_all) {
         else LAUNCH(e, k_sort_small<false>, 1, kRgThreads, 0, SMALL_ARGS);
 #undef SMALL_ARGS
         CK(cudaGetLastError());
+        if (box_in_sort) e->bbox_valid = true;
         return finish_sort(e, nxt);
     }
     LAUNCH(e, k_grid_setup, setup_blocks, 256, 0, e->c, e->d_bbox, e->d_grid, e->cell_start.p);
