@@ -381,6 +381,10 @@ int sphb_multi_step(sphb_multi* m, int nsteps);          /* asynchronous */
 int sphb_multi_synchronize(sphb_multi* m);
 int sphb_multi_download_aos(sphb_multi* m, void* particles, size_t n, size_t stride, uint32_t field_mask);
 int sphb_multi_step_aos(sphb_multi* m, void* particles, size_t n, size_t stride, int nsteps, uint32_t field_mask);
+/* The slab cuts sphb_multi_upload_aos would choose for these x coordinates (host arithmetic only, no GPU involved): ndev+1
+ * increasing values, the first and last being the smallest and largest x; inner cuts sit on multiples of h*h from the first and
+ * equalise owned-plus-ghost particle counts (ghost layers 2 h*h wide). */
+int sphb_multi_plan(const float* x, size_t n, int ndev, float h, double* bounds);
 /* ndev, per-GPU record counts (owned + ghosts; synchronises), and the ndev+1 slab cuts.  Any pointer may be NULL. */
 int sphb_multi_info(sphb_multi* m, int* ndev, size_t* owned_plus_ghosts, double* bounds);
 

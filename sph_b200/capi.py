@@ -79,7 +79,7 @@ EXPORTS = [
     "sphb_get_device_state", "sphb_stream", "sphb_bbox_noalloc", "sphb_download_soa",
     "sphb_count_nonfinite", "sphb_default_camera", "sphb_render_depth", "sphb_download_positions", "sphb_set_spheres", "sphb_get_spheres", "sphb_mg_message_bytes", "sphb_reserve", "sphb_mg_pack", "sphb_mg_pack_limits", "sphb_mg_unpack", "sphb_mg_sent", "sphb_get_stats", "sphb_mg_unpack_async", "sphb_mg_poll", "sphb_mg_link_create", "sphb_mg_link_destroy", "sphb_mg_link_export",
     "sphb_mg_link_connect_ipc", "sphb_mg_link_connect_local", "sphb_mg_exchange", "sphb_set_ids", "sphb_multi_create", "sphb_multi_destroy", "sphb_multi_last_error", "sphb_multi_set_walls",
-    "sphb_multi_upload_aos", "sphb_multi_step", "sphb_multi_synchronize", "sphb_multi_download_aos", "sphb_multi_step_aos", "sphb_multi_info",
+    "sphb_multi_upload_aos", "sphb_multi_step", "sphb_multi_synchronize", "sphb_multi_download_aos", "sphb_multi_step_aos", "sphb_multi_info", "sphb_multi_plan",
 ]
 
 _lib = None
@@ -168,6 +168,7 @@ def load_library() -> C.CDLL:
     L.sphb_multi_download_aos.argtypes = [vp, vp, sz, sz, u32]
     L.sphb_multi_step_aos.argtypes = [vp, vp, sz, sz, i32, u32]
     L.sphb_multi_info.argtypes = [vp, C.POINTER(i32), vp, vp]
+    L.sphb_multi_plan.argtypes = [vp, sz, i32, C.c_float, vp]
     _lib = L
     return L
 
@@ -198,6 +199,17 @@ def _ptr(a):
     if isinstance(a, int):
         return C.c_void_p(a)
     return a.ctypes.data_as(C.c_void_p)
+
+
+def multi_plan(x: np.ndarray, ndev: int, h: float = 0.45):
+    """The slab cuts sphb_multi_upload_aos would choose for these x coordinates (host arithmetic, no GPU)."""
+    L = load_library()
+    x = np.ascontiguousarray(x, np.float32)
+    b = np.zeros(ndev + 1, np.float64)
+    rc = L.sphb_multi_plan(_ptr(x), len(x), ndev, C.c_float(h), _ptr(b))
+    if rc:
+        raise SphbError(f"sphb error {rc}: {L.sphb_multi_last_error().decode()}")
+    return b
 
 
 class Multi:

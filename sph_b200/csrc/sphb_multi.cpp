@@ -103,6 +103,16 @@ extern "C" {
 
 const char* sphb_multi_last_error(void) { return g_merr; }
 
+int sphb_multi_plan(const float* x, size_t n, int ndev, float h, double* bounds) {
+    if (!bounds || (n && !x)) return mfail(SPHB_ERR_INVALID, "null argument");
+    if (ndev < 1 || ndev > 64) return mfail(SPHB_ERR_INVALID, "ndev must be in [1, 64]");
+    if (!(h > 0.0f)) return mfail(SPHB_ERR_INVALID, "h must be positive");
+    const double R = (double)(h * h);
+    const std::vector<double> b = balanced_bounds(std::vector<float>(x, x + n), ndev, R, 2.0 * R * 1.001);
+    for (int k = 0; k <= ndev; k++) bounds[k] = b[k];
+    return SPHB_OK;
+}
+
 int sphb_multi_create(int ndev, const int* devices, const sphb_params* p, sphb_multi** out) {
     if (!p || !out) return mfail(SPHB_ERR_INVALID, "null argument");
     if (ndev < 1 || ndev > 64) return mfail(SPHB_ERR_INVALID, "ndev must be in [1, 64]");

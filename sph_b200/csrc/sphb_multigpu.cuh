@@ -234,6 +234,10 @@ __global__ void __launch_bounds__(kMgThreads) k_mg_write(Slab s, float4* __restr
     const int ntiles = (n + kMgTile - 1) / kMgTile;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int i0 = tile * kMgTile + threadIdx.x * kMgPer;
+        // a tile none of whose eight warps has anything to do (away from the slab faces: nine tiles in ten) is left at once,
+        // before the block scan and its barriers
+        static_assert(kMgThreads / 32 == 8, "one 8-byte load covers a tile's touch flags");
+        if (*reinterpret_cast<const unsigned long long*>(touch + (size_t)tile * 8) == 0ull) continue;
         const bool active = touch[tile * (kMgThreads / 32) + (threadIdx.x >> 5)] != 0; // warp-uniform
         // phase 1: this thread's record counts (nothing is kept in registers: phase 2 reads the four particles again,
         // from L1 -- holding them cost 107 registers and three quarters of the occupancy)

@@ -76,3 +76,31 @@ def test_scene_generators():
     assert len(np.unique(ps["pos"], axis=0)) == len(ps)
     ps2, _ = scenes.block_drop(scale=16)
     assert len(ps2) == 2 ** 24 // 16 ** 3
+
+
+def test_multi_gpu_slab_plan_balances_owned_plus_ghost_counts():
+    """sphb_multi_plan (the C++ restatement of multigpu.balanced_bounds that sphb_multi_upload_aos uses; host arithmetic, no GPU):
+    on a lumpy distribution the cuts are increasing, sit on multiples of the support radius from the left-most particle, give
+    every rank work -- its own particles plus the 2R ghost layers -- within 15 % of the mean, and do at least as well as plain
+    particle-count quantiles."""
+    from sph_b200 import multigpu
+    rng = np.random.default_rng(4)
+    x = np.concatenate([rng.uniform(0, 26, 300_000), rng.uniform(9, 16, 500_000), rng.normal(13, 0.5, 200_000)]).astype(np.float32)
+    R = multigpu.support_radius()
+    halo = 2 * R * 1.001
+    xs = np.sort(x.astype(np.float64))
+    load = lambda b: np.array([np.searchsorted(xs, np.float32(b[r + 1] + (halo if r < len(b) - 2 else 1e30))) -
+                               np.searchsorted(xs, np.float32(b[r] - (halo if r else 1e30))) for r in range(len(b) - 1)], np.float64)
+    for world in (2, 4, 8):
+        b = capi.multi_plan(x, world)
+        assert len(b) == world + 1 and b[0] == x.min() and b[-1] == x.max()
+        assert np.all(np.diff(b) > 0)
+        k = (b[1:-1] - b[0]) / R
+        assert np.allclose(k, np.round(k), atol=1e-6)
+        w = load(b)
+        assert w.max() / w.mean() <= 1.15, (world, w)
+        q = multigpu.quantile_bounds(x, world, R, float(x.min()), float(x.max()))
+        assert w.max() <= load(q).max() * 1.02
+    assert list(capi.multi_plan(x, 1)) == [float(x.min()), float(x.max())]
+    with pytest.raises(sph_b200.SphbError):
+        capi.multi_plan(x, 0)
