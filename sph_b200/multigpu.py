@@ -349,7 +349,22 @@ def setup_slab_run(mode, scale, world, rank, local, accel=True, transport="nccl"
                 else f"block drop into tank (config 4 pattern), one tank section of {n_own} particles per GPU ({world} sections side by side)")
     sr = SlabRank(eng, slab, capacity, local, transport=transport)
     if transport == "p2p":
-        sr.connect(dist, rank, world, left, right)
+        # every rank must end up on the same transport: if mapping a neighbour's block fails anywhere (no peer access, IPC
+        # forbidden in this container, ...), all ranks fall back to NCCL message buffers together
+        ok = 1
+        try:
+            sr.connect(dist, rank, world, left, right)
+        except capi.SphbError as err:
+            ok = 0
+            print(f"[rank {rank}] peer-to-peer halo link unavailable ({err}); falling back to NCCL send/recv", flush=True)
+        if world > 1:
+            import torch
+            flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok = int(flag.item())
+        if not ok:
+            sr.close()
+            sr = SlabRank(eng, slab, capacity, local, transport="nccl")
     return eng, sr, ps, (left, right), what, capacity
 
 
@@ -426,7 +441,7 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
     parts = np.zeros(3)
     nb = 4
     for _ in range(nb):
-        if transport == "p2p":           # one call: pack into the neighbours' buffers, flags, append; only the whole is timed
+        if sr.transport == "p2p":           # one call: pack into the neighbours' buffers, flags, append; only the whole is timed
             sr.poll()
             ev[0].record(sr.stream)
             sr.exchange_p2p()
@@ -454,9 +469,9 @@ def run_slab_workload(args, mode, scale, world, rank, local, dist, steps, warmup
            "ms_per_step": ms / steps, "value": value, "gpu_launches": launches_all,
            "phase_ms": {"sort": float(phase[0]), "density": float(phase[1]), "force": float(phase[2]), "engine_step_rank0": float(phase[3]),
                         "engine_step_max_over_ranks": float(step_max.item()),
-                        "breakdown_rank0": ({"exchange_p2p (pack + flags + append)": float(parts[0])} if transport == "p2p" else
+                        "breakdown_rank0": ({"exchange_p2p (pack + flags + append)": float(parts[0])} if sr.transport == "p2p" else
                                             {"pack": float(parts[0]), "send_recv": float(parts[1]), "unpack": float(parts[2])})},
-           "transport": transport,
+           "transport": sr.transport,
            "exchange_exposed_ms": ms / steps - float(step_max.item()),
            "halo": {"counts_rank0": {"kept": sr.counts[0], "from_left": sr.counts[1], "from_right": sr.counts[2]}, "message_capacity": capacity},
            "local_particles_incl_ghosts_rank0": eng.count(), "clocks": clocks, "_phase": phase}
@@ -608,7 +623,7 @@ def bench_main(args, world, rank, local):
             "config": {"workload": head["workload"], "particles": head["particles"], "particles_per_gpu": head["particles_per_gpu_rank0"],
                        "decomposition": "x slabs, halo = 2 support radii, one exchange with each x-neighbour per step",
                        "transport": ("pack kernel writes into the neighbours' receive buffers over NVLink peer memory (CUDA IPC), flag kernels"
-                                     if getattr(args, "transport", "nccl") == "p2p" else "NCCL send/recv of message buffers (torch.distributed)"),
+                                     if head.get("transport") == "p2p" else "NCCL send/recv of message buffers (torch.distributed)"),
                        "l2": "state exceeds the 126 MB L2", "accel_output": not args.no_accel, "reset_every": reset},
             "clocks": head["clocks"], "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
             "phase_ms": head["phase_ms"], "exchange_exposed_ms": head["exchange_exposed_ms"], "halo": head["halo"],
