@@ -52,6 +52,10 @@ struct Consts {
     float dom_lo[3], dom_hi[3];
     long long max_cells;
     float lap_coef; // coefficient of the optional Laplacian viscosity (SphUtils.cpp:277), 0 when off
+    // Multi-GPU: the box outside which nobody needs a particle's density -- the slab (and the periodic box) grown by ONE support
+    // radius.  Ghost layers are two radii wide so that the inner half can have its density recomputed here; the outer half is
+    // only ever a neighbour in that sum, never a target.  (-inf, +inf) on an engine that exchanges no slabs.
+    float need_lo[3], need_hi[3];
     float cell;   // cell edge in y and z
     float cell_x; // cell edge in x (cell / cell_x_div)
     int stencil_x;

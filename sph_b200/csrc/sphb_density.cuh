@@ -317,6 +317,15 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
         pi[k] = ldg4(posm + i0 + min(k, nt - 1));
         cell_key(g, pi[k].x, pi[k].y, pi[k].z, cx[k], cy[k], cz[k]);
     }
+    {   // outer ghosts (more than a support radius outside the slab or the periodic box): nobody reads their density, masks or
+        // (vx, vy, vz, rho) record -- the fused force kernel passes ghosts through -- so a group made of them is left at once
+        bool needed = false;
+#pragma unroll
+        for (int k = 0; k < kDT; k++)
+            needed |= pi[k].x >= c.need_lo[0] && pi[k].x < c.need_hi[0] && pi[k].y >= c.need_lo[1] && pi[k].y < c.need_hi[1] &&
+                      pi[k].z >= c.need_lo[2] && pi[k].z < c.need_hi[2];
+        if (!needed) return;
+    }
     const int S = g.stencil, Sx = g.stencil_x;
     const int nrows = (2 * S + 1) * (2 * S + 1);
     float sum[kDT] = {0.0f, 0.0f, 0.0f, 0.0f};

@@ -12,6 +12,10 @@
 
 using namespace sphb;
 
+#ifndef SPHB_BBOX_FUSED
+#define SPHB_BBOX_FUSED 0 /* 1: track the bounding box of the new positions inside the fused force kernel (measured slower, see sphb_step) */
+#endif
+
 namespace {
 
 thread_local char g_err[512] = "";
@@ -176,6 +180,7 @@ void build_consts(sphb_engine* e) {
         c.dom_hi[a] = p.domain_hi[a];
     }
     c.lap_coef = p.laplacian_viscosity ? p.lap_visc_coef : 0.0f;
+    for (int a = 0; a < 3; a++) { c.need_lo[a] = -INFINITY; c.need_hi[a] = INFINITY; }
     c.cell = p.cell_size > 0.0f ? p.cell_size : c.h2;
     const int div = p.cell_x_div > 0 ? p.cell_x_div : 2;
     c.cell_x = c.cell / (float)div;
@@ -227,6 +232,17 @@ int run_bbox(sphb_engine* e) {
     e->bbox_valid = true;
     CK(cudaGetLastError());
     return SPHB_OK;
+}
+
+// densities are needed inside the slab (and the periodic box) grown by one support radius: see Consts::need_lo
+void set_need_box(sphb_engine* e, const sphb_slab* s) {
+    const float R = e->c.h2;
+    for (int a = 0; a < 3; a++) { e->c.need_lo[a] = -INFINITY; e->c.need_hi[a] = INFINITY; }
+    if (!s) return;
+    e->c.need_lo[0] = s->lo - R;
+    e->c.need_hi[0] = s->hi + R;
+    if (s->periodic_y) { e->c.need_lo[1] = s->ylo - R; e->c.need_hi[1] = s->ylo + s->ylen + R; }
+    if (s->periodic_z) { e->c.need_lo[2] = s->zlo - R; e->c.need_hi[2] = s->zlo + s->zlen + R; }
 }
 
 // the device-side particle count the kernels should use instead of their n argument (null: the host's n is exact)
@@ -313,25 +329,35 @@ int run_sort(sphb_engine* e, bool carry_all) {
 // K4.  with_aux = false only rebuilds the neighbour masks (update_forces on an uploaded rho/P).
 constexpr int kSmallScene = 32768; // particles up to which the latency-oriented kernel variants are used
 
-int run_density(sphb_engine* e, bool with_aux) {
+// The fused step of an engine that exchanges slabs treats ghosts specially (force kernel: passed through; density kernel: the
+// outer half of the ghost layers skipped) -- only in the configuration both kernels have that variant for.
+bool ghost_path(const sphb_engine* e, int n) {
+    const bool bbox_fused = SPHB_BBOX_FUSED && !e->c.domain_fixed;
+    return e->mg_used && e->rows == 9 && !bbox_fused && (n > kSmallScene || e->n_deferred);
+}
+
+int run_density(sphb_engine* e, bool with_aux, bool skip_outer_ghosts = false) {
     const int n = (int)e->n;
     if (n == 0) return SPHB_OK;
+    Consts c = e->c;
+    if (!skip_outer_ghosts)
+        for (int a = 0; a < 3; a++) { c.need_lo[a] = -INFINITY; c.need_hi[a] = INFINITY; }
     // groups <= n/kDT + (number of non-empty rows); threads beyond the device-side total exit at once
     long long rows_bound = e->max_cells < kMaxRows ? e->max_cells : kMaxRows;
     if (rows_bound > n) rows_bound = n;
     const long long groups = cdiv(n, kDT) + rows_bound;
     if (n <= kSmallScene && e->rows == 9 && !e->n_deferred) { // small scene: a group's rows side by side on 16 lanes (latency, not throughput)
         auto kfs = with_aux ? k_density<true, true, 16> : k_density<false, true, 16>;
-        LAUNCH(e, kfs, cdiv(groups * 16, 128), 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+        LAUNCH(e, kfs, cdiv(groups * 16, 128), 128, 0, c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
                e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, (int)e->mstride, 0);
     } else {
         auto kfn = with_aux ? k_density<true, true> : k_density<false, true>;
         const int blocks = cdiv(groups, 128);
-        LAUNCH(e, kfn, blocks, 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+        LAUNCH(e, kfn, blocks, 128, 0, c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
                e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, (int)e->mstride, 0);
         if (e->n_deferred) { // n was an estimate: a few blocks walk whatever groups lie beyond the main launch (normally none)
             auto ktail = with_aux ? k_density<true, true, 1, true> : k_density<false, true, 1, true>;
-            LAUNCH(e, ktail, 148, 128, 0, e->c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
+            LAUNCH(e, ktail, 148, 128, 0, c, e->d_grid, e->cell_start.p, e->row_groups.p, e->posm[e->cur].p,
                    e->vel[e->cur].p, e->aux[e->cur].p, e->vr.p, e->mask.p, (int)e->mstride, blocks * 128);
         }
     }
@@ -599,6 +625,7 @@ int sphb_upload_aos(sphb_engine* e, const void* particles, size_t n, size_t stri
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    set_need_box(e, nullptr);
     e->mg_used = false;
     e->global_ids = false;
     e->n_dead = 0;
@@ -653,6 +680,7 @@ int sphb_upload_soa_device(sphb_engine* e, const void* posm, const void* vel, co
         CK(cudaGetLastError());
     }
     e->have_state = true;
+    set_need_box(e, nullptr);
     e->mg_used = false;
     e->global_ids = false;
     e->n_dead = 0;
@@ -889,9 +917,6 @@ int sphb_step(sphb_engine* e, int nsteps) {
     // Bounding-box grid mode: the box of the new positions comes from one streaming pass at the start of the next sort (k_bbox,
     // 16 B/particle: 0.05 ms at 16.7 M).  Tracking it inside the fused force kernel instead (SPHB_BBOX_FUSED=1: per-warp boxes,
     // joined by k_bbox_fold) costs that kernel six live registers and 0.17 ms; earlier forms of the fold cost 0.36 - 0.5 ms.
-#ifndef SPHB_BBOX_FUSED
-#define SPHB_BBOX_FUSED 0
-#endif
     const bool bbox = SPHB_BBOX_FUSED && !e->c.domain_fixed;
     const bool acc = e->params.write_accel != 0;
     if (e->params.laplacian_viscosity || e->params.parity_mode) { // optional extra force pass / reference-order arithmetic: run the phases one by one
@@ -909,7 +934,7 @@ int sphb_step(sphb_engine* e, int nsteps) {
         const int n = (int)e->n; // after the sort: records marked dead by the slab exchange are gone
         if (n == 0) return SPHB_OK;
         if (timed) CK(cudaEventRecord(ev[1], e->stream));
-        if ((rc = run_density(e, true))) return rc;
+        if ((rc = run_density(e, true, ghost_path(e, n)))) return rc;
         if (timed) CK(cudaEventRecord(ev[2], e->stream));
         const int cur = e->cur, nxt = cur ^ 1;
         const int blocks = cdiv(n, 128);
@@ -920,7 +945,7 @@ int sphb_step(sphb_engine* e, int nsteps) {
             kfn = bbox ? (acc ? k_force<true, true, true, 9, true, 4> : k_force<true, true, false, 9, true, 4>)
                        : (acc ? k_force<true, false, true, 9, true, 4> : k_force<true, false, false, 9, true, 4>);
         // an engine that exchanges slabs holds ghosts: the variant that passes them through (big scenes, 9-row stencil, no bbox fold)
-        const bool ghosts = e->mg_used && e->rows == 9 && !bbox && (n > kSmallScene || e->n_deferred);
+        const bool ghosts = ghost_path(e, n);
         if (ghosts) kfn = acc ? k_force<true, false, true, 9, true, 1, false, true> : k_force<true, false, false, 9, true, 1, false, true>;
         LAUNCH(e, kfn, blocks, 128, 0, FORCE_ARGS, 0);
         int box_records = bbox ? blocks * 4 : 0;
@@ -1312,6 +1337,7 @@ int unpack_async_impl(sphb_engine* e, const sphb_slab* slab, const void* from_le
     if (!e->mg_pending) return fail(SPHB_ERR_STATE, "sphb_mg_unpack_async without sphb_mg_pack");
     if ((rc = prepare_exchange(e))) return rc;
     const Slab s = to_slab(slab);
+    set_need_box(e, slab);
     const int cur = e->cur;
     int* totals = e->mg_counts.p + kMgStreams * e->mg_blocks;
     int* recv = totals + 4;
@@ -1365,6 +1391,7 @@ extern "C" int sphb_mg_unpack(sphb_engine* e, const sphb_slab* slab, const void*
     s.shift_left = slab->shift_left; s.shift_right = slab->shift_right;
     s.per_y = slab->periodic_y; s.per_z = slab->periodic_z;
     s.ylo = slab->ylo; s.ylen = slab->ylen; s.zlo = slab->zlo; s.zlen = slab->zlen;
+    set_need_box(e, slab);
     const int cur = e->cur; // the kept particles stayed in place: everything is appended behind them
     int* totals = e->mg_counts.p + kMgStreams * e->mg_blocks;
     int* recv = totals + 4;
