@@ -288,25 +288,51 @@ __device__ __forceinline__ void density_row_single(const Consts& c, const float4
 #ifndef SPHB_DENSITY_WFORM
 #define SPHB_DENSITY_WFORM 1
 #endif
+#ifndef SPHB_DENSITY_TILE
+#define SPHB_DENSITY_TILE 0
+#endif
 #ifndef SPHB_DENSITY_MINBLOCKS
 #define SPHB_DENSITY_MINBLOCKS 8
 #endif
 // kLanes: 1, or 16 for small scenes: the 9 rows of a group go to 9 of 16 consecutive lanes (partial sums joined by
 // shuffles, each lane writes its own row's mask words), because with a few hundred groups the GPU is empty and what
 // counts is the length of one thread's chain: 972 particles (main.cpp's scene) 30 us -> see DESIGN.md.
-template <bool kAux, bool kMask, int kLanes>
+// kTile (experiment, SPHB_DENSITY_TILE): the warp stages the union of its lanes' candidate runs of each stencil row in a
+// shared-memory tile (coalesced loads, 16-byte records XOR-swizzled so that lanes four records apart read different bank
+// groups) and the candidate loop reads LDS.128 instead of LDG.128.  All 32 lanes then stay in the row loop together.
+#if SPHB_DENSITY_TILE == 3
+constexpr int kTileRecs = 160; // records per warp tile buffer (2.5 KB; two buffers per warp: the next row is copied while this one is read)
+#else
+constexpr int kTileRecs = 256; // records per warp tile (4 KB)
+#endif
+__device__ __forceinline__ int tile_swz(int k) { return k ^ ((k >> 3) & 7); }
+__device__ __forceinline__ unsigned int smem_u32(const void* p) { return (unsigned int)__cvta_generic_to_shared(p); }
+// bounded wait for the phase of an mbarrier (a lost copy must not hang the GPU: the caller then reads whatever is there and the
+// parity tests fail loudly)
+__device__ __forceinline__ bool mbar_wait(unsigned int bar, unsigned int parity) {
+    for (int it = 0; it < (1 << 22); it++) {
+        unsigned int ok;
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return true;
+    }
+    return false;
+}
+
+template <bool kAux, bool kMask, int kLanes, bool kTile = false>
 __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& g, const int* __restrict__ cell_start,
                                                const int* __restrict__ gstart,
                                                const float4* __restrict__ posm, const float4* __restrict__ vel,
                                                float4* __restrict__ aux, float4* __restrict__ vr,
                                                unsigned int* __restrict__ mask, const int n /* mask stride */, const int tg,
-                                               const int nrows_grid, const int ngroups) {
+                                               const int nrows_grid, const int ngroups, float4* tile = nullptr,
+                                               unsigned long long* bars = nullptr, int* meta = nullptr) {
     const int t_raw = tg / kLanes, sub = tg % kLanes; // group, and which of its rows this lane takes (kLanes > 1)
     if ((tg & ~31) / kLanes >= ngroups) return;    // whole warp beyond the last group
     const bool live = t_raw < ngroups;
     const int t = live ? t_raw : ngroups - 1;       // spare lanes of the last warp shadow the last group (warp-wide votes below)
     const int lo_r = find_row(gstart, nrows_grid, t);
-    if (!live) return;
+    bool active = live;                             // kTile: lanes without work stay for the warp-wide staging
+    if (!kTile && !live) return;
     const int row_end = __ldg(cell_start + (lo_r + 1) * g.dims[0]);
     const int i0 = __ldg(cell_start + lo_r * g.dims[0]) + (t - __ldg(gstart + lo_r)) * kDT;
     const int nt = min(kDT, row_end - i0); // the tail group of a row is short: extra targets repeat the last one
@@ -324,8 +350,11 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
         for (int k = 0; k < kDT; k++)
             needed |= pi[k].x >= c.need_lo[0] && pi[k].x < c.need_hi[0] && pi[k].y >= c.need_lo[1] && pi[k].y < c.need_hi[1] &&
                       pi[k].z >= c.need_lo[2] && pi[k].z < c.need_hi[2];
-        if (!needed) return;
+        if (!kTile && !needed) return;
+        active = active && needed;
     }
+    // kTile: the tile holds ONE contiguous run per stencil row, which needs every lane of the warp to work on the same row of cells
+    const bool same_row = kTile ? __all_sync(0xffffffffu, lo_r == __shfl_sync(0xffffffffu, lo_r, 0)) : false;
     const int S = g.stencil, Sx = g.stencil_x;
     const int nrows = (2 * S + 1) * (2 * S + 1);
     float sum[kDT] = {0.0f, 0.0f, 0.0f, 0.0f};
@@ -335,6 +364,37 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
         const float2 nx23 = make_float2(-pi[2].x, -pi[3].x), ny23 = make_float2(-pi[2].y, -pi[3].y), nz23 = make_float2(-pi[2].z, -pi[3].z);
         const float2 nR2 = make_float2(-c.R2, -c.R2), nih2 = make_float2(-c.inv_h2, -c.inv_h2);
         float2 acc01 = make_float2(0.0f, 0.0f), acc23 = make_float2(0.0f, 0.0f);
+#if SPHB_DENSITY_TILE == 3
+        // TMA variant: the union of the warp's candidate runs of a stencil row is ONE contiguous run of the sorted array between two
+        // x-cells that are the same for all nine rows; lane 0 copies it into the warp's tile with one cp.async.bulk (completion on
+        // an mbarrier), a row ahead of its use, into the buffer the row before last has just been read from
+        int x0W = 0, x1W = -1;
+        unsigned int ph = 0; // phase parity of the two barriers
+        bool tma_ok = false;
+        auto tma_issue = [&](int r, int buf) { // lane 0 only
+            const int W = 2 * S + 1, z = cz[0] + r / W - S, y = cy[0] + r % W - S;
+            int jb = -1;
+            if (!(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1])) {
+                const int row = g.dims[0] * (y + g.dims[1] * z);
+                const int b = __ldg(cell_start + row + x0W), e = __ldg(cell_start + row + x1W + 1);
+                if (e > b && e - b <= kTileRecs) {
+                    jb = b;
+                    const unsigned int bytes = (unsigned int)(e - b) * 16u, bar = smem_u32(bars + buf), dst = smem_u32(tile + buf * kTileRecs);
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(posm + b),
+                                 "r"(bytes), "r"(bar)
+                                 : "memory");
+                }
+            }
+            meta[buf] = jb;
+        };
+        if (kTile) {
+            x0W = __reduce_min_sync(0xffffffffu, active ? max(cxlo - Sx, 0) : 0x7fffffff);
+            x1W = __reduce_max_sync(0xffffffffu, active ? min(cxhi + Sx, g.dims[0] - 1) : -1);
+            tma_ok = same_row && x1W >= x0W;
+            if (tma_ok && (threadIdx.x & 31) == 0) tma_issue(0, 0);
+        }
+#endif
         // rows in canonical order r = (dz+S)*(2S+1) + (dy+S), counted without the divisions a runtime stencil would cost
         int dy_r = -S, dz_r = -S;
         unsigned int* mrow = mask + i0 + 2 * (size_t)n * (kLanes > 1 ? sub : 0); // word w of row r of target k: mrow[(2r+w)*n + k]
@@ -343,13 +403,41 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
             const int z = cz[0] + dz_r, y = cy[0] + dy_r;
             if (kLanes == 1 && ++dy_r > S) { dy_r = -S; ++dz_r; }
             int jbu = 0, jeu = 0, jbk[kDT] = {0, 0, 0, 0};
-            const bool inside = !(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]);
+            const bool inside = (!kTile || active) && !(z < 0 || z >= g.dims[2] || y < 0 || y >= g.dims[1]);
             if (inside) {
                 const int row = g.dims[0] * (y + g.dims[1] * z);
                 jbu = __ldg(cell_start + row + max(cxlo - Sx, 0));
                 jeu = __ldg(cell_start + row + min(cxhi + Sx, g.dims[0] - 1) + 1);
 #pragma unroll
                 for (int k = 0; k < kDT; k++) jbk[k] = (cx[k] == cxlo) ? jbu : __ldg(cell_start + row + max(cx[k] - Sx, 0));
+            }
+            int jbW = 0;
+            bool use_tile = false;
+#if SPHB_DENSITY_TILE == 3
+            if (kTile && tma_ok) {
+                __syncwarp(); // every lane is done with the row before: its buffer may be overwritten
+                if ((threadIdx.x & 31) == 0 && r + 1 < nrows) tma_issue(r + 1, (r + 1) & 1);
+                __syncwarp();
+                jbW = meta[r & 1];
+                if (jbW >= 0) {
+                    mbar_wait(smem_u32(bars + (r & 1)), (ph >> (r & 1)) & 1u);
+                    ph ^= 1u << (r & 1);
+                    use_tile = true;
+                }
+            }
+            if (false) {
+#else
+            if (kTile) { // stage the union of the lanes' runs of this row
+#endif
+                const bool plain = inside && jeu > jbu && jeu - jbu <= kMaskBits;
+                jbW = __reduce_min_sync(0xffffffffu, plain ? jbu : 0x7fffffff);
+                const int jeW = __reduce_max_sync(0xffffffffu, plain ? jeu : 0);
+                use_tile = same_row && jeW > jbW && jeW - jbW <= kTileRecs;
+                if (use_tile) {
+                    __syncwarp(); // the previous row's readers are done
+                    for (int k = threadIdx.x & 31; k < jeW - jbW; k += 32) tile[SPHB_DENSITY_TILE == 2 ? k : tile_swz(k)] = ldg4(posm + jbW + k);
+                    __syncwarp();
+                }
             }
             if (jeu - jbu > kMaskBits) { // crowded union: per-target general path for this row
 #pragma unroll
@@ -416,12 +504,23 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
                 if (len > 0) {
                     // software pipeline: the next pair's loads are in flight during this pair's arithmetic (2.14 -> 2.08 ms
                     // at 16.7 M; only with all 8 blocks resident -- at 80 or 96 registers it loses more than it gains)
-                    float4 q0 = ldg4(posm + ja), q1 = ldg4(posm + min(ja + 1, jz - 1));
+#if SPHB_DENSITY_TILE == 3
+                    const float4* src = (kTile && use_tile) ? (const float4*)tile + (r & 1) * kTileRecs - jbW : posm;
+                    auto cand = [&](int j) -> float4 { return kTile ? src[j] : ldg4(posm + j); };
+#elif SPHB_DENSITY_TILE == 2
+                    // plain tile layout, one loop for both sources: a generic pointer that is either the tile shifted by the union's
+                    // first slot or the global array (no swizzle arithmetic, no second code path)
+                    const float4* src = (kTile && use_tile) ? (const float4*)tile - jbW : posm;
+                    auto cand = [&](int j) -> float4 { return kTile ? src[j] : ldg4(posm + j); };
+#else
+                    auto cand = [&](int j) -> float4 { return (kTile && use_tile) ? tile[tile_swz(j - jbW)] : ldg4(posm + j); };
+#endif
+                    float4 q0 = cand(ja), q1 = cand(min(ja + 1, jz - 1));
                     for (int j = ja; j < jz; j += 2) {
                         const bool two = j + 1 < jz;
                         const float4 p0 = q0, p1 = q1;
-                        q0 = ldg4(posm + min(j + 2, jz - 1));
-                        q1 = ldg4(posm + min(j + 3, jz - 1));
+                        q0 = cand(min(j + 2, jz - 1));
+                        q1 = cand(min(j + 3, jz - 1));
                         test4(p0, p0.w);
                         test4(p1, two ? p1.w : 0.0f);
                     }
@@ -441,7 +540,7 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
                     m64 >>= (jbk[k] - jbu); // union-relative -> relative to this target's own run
                     const int self = i0 + k - jbk[k];
                     if (r == (nrows >> 1) && self >= 0 && self < kMaskBits) m64 &= ~(1ull << self); // self excluded by index
-                    if (k < nt) {
+                    if (k < nt && (!kTile || active)) { // kTile: lanes that only help with the staging write nothing
                         mrow[k] = (unsigned int)m64;
                         mrow[(size_t)n + k] = (unsigned int)(m64 >> 32);
                     }
@@ -465,6 +564,7 @@ __device__ __forceinline__ void density_thread(const Consts& c, const GridDesc& 
             for (int o = kLanes / 2; o > 0; o >>= 1) sum[k] += __shfl_xor_sync(am, sum[k], o);
         if (sub != 0) return;
     }
+    if (kTile && !active) return;
     if (kAux) {
 #pragma unroll
         for (int k = 0; k < kDT; k++) {
@@ -496,6 +596,31 @@ __global__ void __launch_bounds__(128, SPHB_DENSITY_MINBLOCKS) k_density(Consts 
     const GridDesc g = *gd;
     const int nrows_grid = g.dims[1] * g.dims[2];
     const int ngroups = __ldg(gstart + nrows_grid);
+#if SPHB_DENSITY_TILE == 3
+    if (!kLoop && kLanes == 1) {
+        __shared__ __align__(128) float4 s_tile[4][2][kTileRecs];
+        __shared__ __align__(8) unsigned long long s_bar[4][2];
+        __shared__ int s_meta[4][2];
+        const int w = threadIdx.x >> 5;
+        if ((threadIdx.x & 31) == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[w][0])) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[w][1])) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            s_meta[w][0] = s_meta[w][1] = -1;
+        }
+        __syncwarp();
+        density_thread<kAux, kMask, kLanes, true>(c, g, cell_start, gstart, posm, vel, aux, vr, mask, n, first + blockIdx.x * blockDim.x + threadIdx.x,
+                                                  nrows_grid, ngroups, &s_tile[w][0][0], s_bar[w], s_meta[w]);
+        return;
+    }
+#elif SPHB_DENSITY_TILE
+    if (!kLoop && kLanes == 1) {
+        __shared__ float4 s_tile[4][kTileRecs];
+        density_thread<kAux, kMask, kLanes, true>(c, g, cell_start, gstart, posm, vel, aux, vr, mask, n, first + blockIdx.x * blockDim.x + threadIdx.x,
+                                                  nrows_grid, ngroups, s_tile[threadIdx.x >> 5]);
+        return;
+    }
+#endif
     if (!kLoop) {
         density_thread<kAux, kMask, kLanes>(c, g, cell_start, gstart, posm, vel, aux, vr, mask, n, first + blockIdx.x * blockDim.x + threadIdx.x, nrows_grid, ngroups);
     } else {
