@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -238,7 +239,7 @@ int run_bbox(sphb_engine* e) {
 void set_need_box(sphb_engine* e, const sphb_slab* s) {
     const float R = e->c.h2;
     for (int a = 0; a < 3; a++) { e->c.need_lo[a] = -INFINITY; e->c.need_hi[a] = INFINITY; }
-    if (!s) return;
+    if (!s || getenv("SPHB_DENSITY_ALL_GHOSTS")) return; // the environment switch is for A/B measurements
     e->c.need_lo[0] = s->lo - R;
     e->c.need_hi[0] = s->hi + R;
     if (s->periodic_y) { e->c.need_lo[1] = s->ylo - R; e->c.need_hi[1] = s->ylo + s->ylen + R; }
